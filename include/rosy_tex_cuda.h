@@ -1,0 +1,185 @@
+/* rosy_tex_cuda.h - C ABI of the B200-native replacement for the Rosy Packager texture stage.
+ *
+ * Drop-in boundary.  The reference links NVTT directly; its texture stage is two
+ * C++ free functions declared at /root/reference/src/Packager/Packager.h:8-9 and defined at
+ * /root/reference/src/Packager/Packager.cpp:216-261 (generate_srgb_texture) and :263-308
+ * (generate_normal_map_texture).  Those two functions keep their signatures and become thin
+ * wrappers over the first two entry points below (INTEGRATION.md shows the patch).  Everything
+ * else here exists for tests, measurement and the multi-GPU work queue.
+ *
+ * Plain C: no C++ types, no exceptions across the boundary, no torch types.  Every function is
+ * thread-safe.  There is NO CPU fallback: without a usable sm_100 device every compute entry
+ * point returns ROSY_TEX_ERR_NO_DEVICE.
+ */
+#ifndef ROSY_TEX_CUDA_H
+#define ROSY_TEX_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(_WIN32)
+#define ROSY_TEX_API __declspec(dllexport)
+#else
+#define ROSY_TEX_API __attribute__((visibility("default")))
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Replaces the `false` returns of nvtt::Surface::load / Context::outputHeader / Context::compress
+ * (Packager.cpp:222-226, :237-241, :245-249); the wrapper maps != 0 to rosy::result::error. */
+typedef enum rosy_tex_status {
+    ROSY_TEX_OK = 0,
+    ROSY_TEX_ERR_IO = 1,        /* cannot read the image / cannot write the .dds */
+    ROSY_TEX_ERR_DECODE = 2,    /* unsupported or corrupt image file */
+    ROSY_TEX_ERR_ARG = 3,       /* null pointer, zero extent, buffer too small, bad enum */
+    ROSY_TEX_ERR_CUDA = 4,      /* a CUDA call failed; see rosy_tex_last_error() */
+    ROSY_TEX_ERR_NO_DEVICE = 5, /* no sm_100 device: there is no CPU fallback */
+    ROSY_TEX_ERR_NOMEM = 6
+} rosy_tex_status;
+
+/* image_type of the .rsy asset, /root/reference/src/Asset/Asset.h:109-112.  Routing follows
+ * src/Packager/Gltf.cpp:225,252,280 and Fbx.cpp:444,453,462: everything except the normal map
+ * goes through the sRGB function. */
+typedef enum rosy_tex_kind {
+    ROSY_TEX_KIND_COLOR = 0,
+    ROSY_TEX_KIND_NORMAL_MAP = 1,
+    ROSY_TEX_KIND_METALLIC_ROUGHNESS = 2,
+    ROSY_TEX_KIND_MIXMAP = 3
+} rosy_tex_kind;
+
+/* nvtt::Format.  The reference only ever uses Format_BC7 (Packager.cpp:229, :276) and the Engine
+ * binds BC7 regardless of the header (src/Engine/Graphics.cpp:3631-3647), so BC7 is the default
+ * for every kind; BC5 / BC4 are opt-in. */
+typedef enum rosy_tex_format {
+    ROSY_TEX_FORMAT_BC7 = 0, /* DXGI_FORMAT_BC7_UNORM (98) */
+    ROSY_TEX_FORMAT_BC5 = 1, /* DXGI_FORMAT_BC5_UNORM (83), channels R,G */
+    ROSY_TEX_FORMAT_BC4 = 2  /* DXGI_FORMAT_BC4_UNORM (80), channel R   */
+} rosy_tex_format;
+
+/* nvtt::Quality_Fastest / Quality_Normal / Quality_Production.  The reference uses Normal
+ * (Packager.cpp:277; NVTT default at :228-229). */
+typedef enum rosy_tex_quality {
+    ROSY_TEX_QUALITY_FAST = 0,
+    ROSY_TEX_QUALITY_NORMAL = 1,
+    ROSY_TEX_QUALITY_HIGH = 2
+} rosy_tex_quality;
+
+/* How nvtt::Surface::normalizeNormalMap (Packager.cpp:295) is read. */
+typedef enum rosy_tex_normalize {
+    ROSY_TEX_NORMALIZE_OFF = 0,   /* literal NVTT-2 reading: no-op on an unflagged surface */
+    ROSY_TEX_NORMALIZE_UNPACK = 1 /* n = 2v-1, n /= |n| (0 if |n| = 0), v = (n+1)/2; default */
+} rosy_tex_normalize;
+
+#define ROSY_TEX_MAX_DEVICES 16
+#define ROSY_TEX_DDS_HEADER_BYTES 148 /* 'DDS ' + DDS_HEADER (124) + DDS_HEADER_DXT10 (20) */
+#define ROSY_TEX_MAX_LEVELS 16
+
+/* Process-wide options.  Zero-initialise, set struct_size, change what you need.
+ * Environment overrides, read by rosy_tex_init (so the Packager CLI stays flag-free):
+ *   ROSY_TEX_DEVICES=0,1,..   ROSY_TEX_QUALITY=fast|normal|high
+ *   ROSY_TEX_FORMAT_NORMAL=bc7|bc5   ROSY_TEX_FORMAT_COLOR=bc7   ROSY_TEX_FORMAT_MR=bc7|bc5|bc4
+ *   ROSY_TEX_NORMALIZE=unpack|off */
+typedef struct rosy_tex_config {
+    uint32_t struct_size;
+    int32_t num_devices;                   /* 0: every visible sm_100 device */
+    int32_t devices[ROSY_TEX_MAX_DEVICES]; /* CUDA ordinals */
+    int32_t quality;                       /* rosy_tex_quality, default NORMAL */
+    int32_t format_for_kind[4];            /* rosy_tex_format per rosy_tex_kind, default BC7 */
+    int32_t normalize;                     /* rosy_tex_normalize, default UNPACK */
+    int32_t streams_per_device;            /* work-queue depth per device, default 2 */
+} rosy_tex_config;
+
+/* One texture.  format / quality / normalize < 0 mean "use the configured default". */
+typedef struct rosy_tex_desc {
+    uint32_t width;
+    uint32_t height;
+    int32_t kind;      /* rosy_tex_kind */
+    int32_t format;    /* rosy_tex_format or -1 */
+    int32_t quality;   /* rosy_tex_quality or -1 */
+    int32_t normalize; /* rosy_tex_normalize or -1 */
+} rosy_tex_desc;
+
+/* ---- lifetime.  init is optional: the first compute call initialises with defaults. ---- */
+ROSY_TEX_API int rosy_tex_init(const rosy_tex_config* config /* may be NULL */);
+ROSY_TEX_API void rosy_tex_shutdown(void);
+ROSY_TEX_API int rosy_tex_device_count(void); /* sm_100 devices in use (0 if none) */
+/* thread-local, never NULL; valid until the next call on this thread */
+ROSY_TEX_API const char* rosy_tex_last_error(void);
+ROSY_TEX_API const char* rosy_tex_status_string(int status);
+
+/* ---- 1:1 with the reference --------------------------------------------------------------
+ * Read the image at image_path (PNG / TGA / PPM / raw .rgba8), build the full mip chain, block
+ * compress every level and write <image_path with its extension replaced by ".dds"> with a
+ * DDS + DX10 header.  Return 0 on success.  The path is borrowed.  The file is written under a
+ * temporary name and renamed, so a failed call leaves no partial .dds behind.
+ *   rosy_tex_generate_srgb_texture        == Packager.cpp:216  generate_srgb_texture
+ *   rosy_tex_generate_normal_map_texture  == Packager.cpp:263  generate_normal_map_texture */
+ROSY_TEX_API int rosy_tex_generate_srgb_texture(const char* image_path);
+ROSY_TEX_API int rosy_tex_generate_normal_map_texture(const char* image_path);
+/* same, with the asset's image_type so that per-kind format overrides apply, and an explicit
+ * output path (NULL: derive as above) */
+ROSY_TEX_API int rosy_tex_generate_texture_file(const char* image_path, int kind,
+                                                const char* dds_path);
+
+/* ---- geometry helpers (nvtt::Surface::countMipmaps, Packager.cpp:235; dds.hpp:527-565) ---- */
+ROSY_TEX_API int rosy_tex_count_mipmaps(uint32_t width, uint32_t height);
+ROSY_TEX_API void rosy_tex_level_extent(uint32_t width, uint32_t height, int level, uint32_t* w,
+                                        uint32_t* h);
+/* bytes of the complete .dds (header + every level) for this descriptor */
+ROSY_TEX_API size_t rosy_tex_dds_size(const rosy_tex_desc* desc);
+/* bytes of the RGBA8 mip chain, level 0 included */
+ROSY_TEX_API size_t rosy_tex_chain_size(uint32_t width, uint32_t height);
+/* writes the 148-byte header (Context::outputHeader, Packager.cpp:237 / :286) */
+ROSY_TEX_API int rosy_tex_dds_header(const rosy_tex_desc* desc, uint8_t* out148);
+
+/* ---- memory to memory (host buffers; H2D, kernels, D2H inside) ---------------------------
+ * rgba: width*height*4 bytes, tightly packed, already decoded.  out receives the whole .dds
+ * image (header + levels, largest first).  The caller owns both buffers; nothing is retained. */
+ROSY_TEX_API int rosy_tex_encode_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out,
+                                       size_t out_capacity, size_t* out_len);
+/* the RGBA8 mip chain exactly as the encoder sees it (what Context::compress quantises to),
+ * level 0 first; for the <= 1 LSB parity check */
+ROSY_TEX_API int rosy_tex_mips_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, uint8_t* out,
+                                     size_t out_capacity, size_t* out_len);
+/* block-compress ONE already built level (no mips, no header); out = raw blocks, row major */
+ROSY_TEX_API int rosy_tex_compress_level_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba,
+                                               void* out, size_t out_capacity, size_t* out_len);
+
+/* ---- asynchronous per-texture work queue over every configured device ------
+ * No collectives: textures are independent.  submit returns at once; results are complete after
+ * wait_all, which returns the first non-zero status of the batch (0 if all succeeded).  For the
+ * memory variant the buffers must stay valid until wait_all returns; *out_len is written by then.
+ * Pinned host buffers (rosy_tex_alloc_host) make the copies asynchronous. */
+ROSY_TEX_API int rosy_tex_submit(const char* image_path, int kind);
+ROSY_TEX_API int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out,
+                                       size_t out_capacity, size_t* out_len);
+ROSY_TEX_API int rosy_tex_wait_all(void);
+ROSY_TEX_API void* rosy_tex_alloc_host(size_t bytes); /* cudaHostAlloc, portable */
+ROSY_TEX_API void rosy_tex_free_host(void* p);
+
+/* ---- device-resident entry points (measurement, callers that already hold device memory) ---
+ * All pointers are device pointers on the CURRENT CUDA device; `stream` is a cudaStream_t
+ * (NULL: legacy default stream).  Nothing synchronises; kernels are only enqueued.
+ *   d_chain  : rosy_tex_chain_size() bytes.  Receives levels 1.. (and level 0 for normal maps,
+ *              whose level 0 is re-normalised); for colour maps level 0 is read from d_rgba.
+ *   d_scratch: rosy_tex_device_scratch_size() bytes.
+ *   d_blocks : rosy_tex_dds_size() - 148 bytes, every level's blocks, largest level first. */
+ROSY_TEX_API size_t rosy_tex_device_scratch_size(const rosy_tex_desc* desc);
+ROSY_TEX_API int rosy_tex_mips_device(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain,
+                                      void* d_scratch, void* stream);
+ROSY_TEX_API int rosy_tex_blocks_device(const rosy_tex_desc* desc, const void* d_rgba,
+                                        const void* d_chain, void* d_blocks, void* stream);
+/* both of the above: the whole hot path with inputs resident in HBM */
+ROSY_TEX_API int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba,
+                                        void* d_chain, void* d_scratch, void* d_blocks,
+                                        void* stream);
+
+/* number of kernels this library has launched since load (all threads, all devices) */
+ROSY_TEX_API uint64_t rosy_tex_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROSY_TEX_CUDA_H */

@@ -1,0 +1,899 @@
+/* bc7.c - CPU ORACLE (test infrastructure, see rosy_oracle.h): BC7 block decoder and encoder.
+ *
+ * Stands in for nvtt::Context::compress(..., Format_BC7) at
+ *   /root/reference/src/Packager/Packager.cpp:245 (colour) and :296 (normal maps)
+ * with nvtt::Quality_Normal (:277 and NVTT's default at :228-229).
+ *
+ * NVTT 3.2.5 is closed source and absent => PARITY UNPINNED for the encoder's
+ * mode / endpoint choices.  What IS fixed by a public document is the block format: the decoder
+ * below follows the BC7 (BPTC) specification and is cross-checked bit for
+ * bit against Pillow's independent BCn decoder in tests/test_oracle_bc7.py.  The encoder is a
+ * scalar statement of the search described in DESIGN.md ("BC7 search, spec v1"): the sm_100a
+ * kernel implements the same specification independently (thread-per-block, dp4a index search)
+ * and is required to match this file's output within 0.1 dB PSNR (and does so bit for bit
+ * today because all decisions are made on integer error sums and ordered fp32 arithmetic).
+ *
+ * Build with -ffp-contract=off: the fp32 expression order below is part of the specification.
+ */
+#include <math.h>
+#include <string.h>
+
+#include "bc7_tables.h"
+#include "rosy_oracle.h"
+
+typedef struct {
+    int ns;  /* subsets */
+    int pb;  /* partition bits */
+    int rb;  /* rotation bits */
+    int isb; /* index-selector bits */
+    int cb;  /* colour bits per endpoint channel */
+    int ab;  /* alpha bits */
+    int epb; /* 1: one p-bit per endpoint */
+    int spb; /* 1: one shared p-bit per subset */
+    int ib;  /* primary index bits */
+    int ib2; /* secondary index bits */
+} mode_info;
+
+static const mode_info MODES[8] = {
+    {3, 4, 0, 0, 4, 0, 1, 0, 3, 0}, {2, 6, 0, 0, 6, 0, 0, 1, 3, 0}, {3, 6, 0, 0, 5, 0, 0, 0, 2, 0},
+    {2, 6, 0, 0, 7, 0, 1, 0, 2, 0}, {1, 0, 2, 1, 5, 6, 0, 0, 2, 3}, {1, 0, 2, 0, 7, 8, 0, 0, 2, 2},
+    {1, 0, 0, 0, 7, 7, 1, 0, 4, 0}, {2, 6, 0, 0, 5, 5, 1, 0, 2, 0},
+};
+
+static const uint8_t W2[4] = {0, 21, 43, 64};
+static const uint8_t W3[8] = {0, 9, 18, 27, 37, 46, 55, 64};
+static const uint8_t W4[16] = {0, 4, 9, 13, 17, 21, 26, 30, 34, 38, 43, 47, 51, 55, 60, 64};
+
+static const uint8_t* weights_for(int ib) { return ib == 2 ? W2 : (ib == 3 ? W3 : W4); }
+
+static int interp(int e0, int e1, int w) { return ((64 - w) * e0 + w * e1 + 32) >> 6; }
+
+static int expand_bits(int v, int bits) {
+    return bits >= 8 ? v : ((v << (8 - bits)) | (v >> (2 * bits - 8)));
+}
+
+static int subset_of(int ns, int partition, int texel) {
+    if (ns == 1) return 0;
+    if (ns == 2) return (BC7_PART2_MASK[partition] >> texel) & 1;
+    return (BC7_PART3_MASK[partition] >> (2 * texel)) & 3;
+}
+
+static void anchors_of(int ns, int partition, int anchor[3]) {
+    anchor[0] = 0;
+    anchor[1] = anchor[2] = -1;
+    if (ns == 2) anchor[1] = BC7_ANCHOR2[partition];
+    if (ns == 3) {
+        anchor[1] = BC7_ANCHOR3A[partition];
+        anchor[2] = BC7_ANCHOR3B[partition];
+    }
+}
+
+/* ------------------------------------------------------------------ decoder */
+
+typedef struct {
+    const uint8_t* d;
+    int pos;
+} bitreader;
+
+static int rd(bitreader* r, int n) {
+    int v = 0;
+    for (int i = 0; i < n; i++, r->pos++) v |= ((r->d[r->pos >> 3] >> (r->pos & 7)) & 1) << i;
+    return v;
+}
+
+int oracle_bc7_block_mode(const uint8_t blk[16]) {
+    if (blk[0] == 0) return -1;
+    int m = 0;
+    while (!((blk[0] >> m) & 1)) m++;
+    return m;
+}
+
+void oracle_bc7_decode_block(const uint8_t blk[16], uint8_t rgba[64]) {
+    int mode = oracle_bc7_block_mode(blk);
+    if (mode < 0) { /* reserved: decoders return zeros */
+        memset(rgba, 0, 64);
+        return;
+    }
+    const mode_info* mi = &MODES[mode];
+    bitreader r = {blk, mode + 1};
+    int partition = rd(&r, mi->pb);
+    int rotation = rd(&r, mi->rb);
+    int idxsel = rd(&r, mi->isb);
+    int ne = 2 * mi->ns;
+    int ep[6][4];
+    for (int c = 0; c < 3; c++)
+        for (int e = 0; e < ne; e++) ep[e][c] = rd(&r, mi->cb);
+    for (int e = 0; e < ne; e++) ep[e][3] = mi->ab ? rd(&r, mi->ab) : 255;
+    int cbits = mi->cb, abits = mi->ab;
+    if (mi->epb || mi->spb) {
+        int pbits[6];
+        if (mi->epb)
+            for (int e = 0; e < ne; e++) pbits[e] = rd(&r, 1);
+        else
+            for (int s = 0; s < mi->ns; s++) pbits[2 * s] = pbits[2 * s + 1] = rd(&r, 1);
+        for (int e = 0; e < ne; e++) {
+            for (int c = 0; c < 3; c++) ep[e][c] = (ep[e][c] << 1) | pbits[e];
+            if (mi->ab) ep[e][3] = (ep[e][3] << 1) | pbits[e];
+        }
+        cbits++;
+        if (abits) abits++;
+    }
+    for (int e = 0; e < ne; e++) {
+        for (int c = 0; c < 3; c++) ep[e][c] = expand_bits(ep[e][c], cbits);
+        if (mi->ab) ep[e][3] = expand_bits(ep[e][3], abits);
+    }
+    int anchor[3];
+    anchors_of(mi->ns, partition, anchor);
+    int idx1[16], idx2[16];
+    for (int i = 0; i < 16; i++) {
+        int is_anchor = (i == anchor[0]) || (i == anchor[1]) || (i == anchor[2]);
+        idx1[i] = rd(&r, mi->ib - is_anchor);
+    }
+    for (int i = 0; i < 16; i++) idx2[i] = mi->ib2 ? rd(&r, mi->ib2 - (i == 0)) : 0;
+    for (int i = 0; i < 16; i++) {
+        int s = subset_of(mi->ns, partition, i);
+        int ci, ai, cw, aw;
+        if (mi->ib2 == 0) {
+            ci = ai = idx1[i];
+            cw = aw = weights_for(mi->ib)[ci];
+        } else if (!idxsel) {
+            ci = idx1[i];
+            ai = idx2[i];
+            cw = weights_for(mi->ib)[ci];
+            aw = weights_for(mi->ib2)[ai];
+        } else {
+            ci = idx2[i];
+            ai = idx1[i];
+            cw = weights_for(mi->ib2)[ci];
+            aw = weights_for(mi->ib)[ai];
+        }
+        int px[4];
+        for (int c = 0; c < 3; c++) px[c] = interp(ep[2 * s][c], ep[2 * s + 1][c], cw);
+        px[3] = interp(ep[2 * s][3], ep[2 * s + 1][3], aw);
+        if (rotation) {
+            int t = px[3];
+            px[3] = px[rotation - 1];
+            px[rotation - 1] = t;
+        }
+        for (int c = 0; c < 4; c++) rgba[4 * i + c] = (uint8_t)px[c];
+    }
+}
+
+/* ------------------------------------------------------------------ encoder */
+
+typedef struct {
+    int n1, n3, n0, n2, n7; /* partitions refined per mode (0 = mode off) */
+    int rot5;               /* rotations tried in mode 5: 1 or 4 */
+    int rot4;               /* rotations tried in mode 4: 0 (off), 1 or 4; both index selectors */
+    int ls_rounds;          /* least-squares refinement rounds per fit */
+    int pb_search;          /* 1: evaluate every p-bit combination, 0: nearest-endpoint p-bits */
+} tier;
+
+/* fast / normal / high  ~  nvtt::Quality_Fastest / Normal / Production */
+static const tier TIERS[3] = {
+    {1, 0, 0, 0, 1, 1, 0, 1, 0},
+    {3, 2, 0, 0, 2, 4, 1, 2, 0},
+    {6, 4, 3, 3, 4, 4, 4, 3, 1},
+};
+
+typedef struct {
+    int q[2][4];  /* quantised endpoint fields (without p-bit) */
+    int pbit[2];
+    int e8[2][4]; /* expanded 8-bit end points */
+    uint8_t idx[16];
+    uint32_t err;
+} fit;
+
+enum { PB_NONE = 0, PB_SHARED = 1, PB_PER_EP = 2 };
+
+typedef struct {
+    int nc;    /* channels that carry data: 1, 3 or 4 (bytes 0..nc-1 of each pixel) */
+    int bits;  /* endpoint field bits */
+    int pbmode;
+    int ib;    /* index bits */
+} fit_cfg;
+
+static float clampf(float x, float lo, float hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
+/* endpoint channel x in [0,255] -> field value with the LSB (p-bit) forced to p */
+static int quant_pbit(float x, int bits, int p) {
+    const int tb = bits + 1;
+    float y = x * ((float)((1 << tb) - 1) / 255.0f);
+    int q = (int)floorf((y - (float)p) * 0.5f + 0.5f);
+    if (q < 0) q = 0;
+    if (q > (1 << bits) - 1) q = (1 << bits) - 1;
+    return q;
+}
+
+static int quant_plain(float x, int bits) {
+    int q = (int)floorf(x * ((float)((1 << bits) - 1) / 255.0f) + 0.5f);
+    if (q < 0) q = 0;
+    if (q > (1 << bits) - 1) q = (1 << bits) - 1;
+    return q;
+}
+
+/* integer SSD of the masked pixels against the palette of (e0,e1); fills idx for those pixels */
+static uint32_t evaluate(const uint8_t px[16][4], int mask, const fit_cfg* cfg, const int e8[2][4],
+                         uint8_t idx[16]) {
+    const int L = 1 << cfg->ib;
+    const uint8_t* W = weights_for(cfg->ib);
+    int pal[16][4];
+    for (int j = 0; j < L; j++)
+        for (int c = 0; c < cfg->nc; c++) pal[j][c] = interp(e8[0][c], e8[1][c], W[j]);
+    uint32_t total = 0;
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        uint32_t best = 0xFFFFFFFFu;
+        int bj = 0;
+        for (int j = 0; j < L; j++) {
+            uint32_t e = 0;
+            for (int c = 0; c < cfg->nc; c++) {
+                int d = (int)px[i][c] - pal[j][c];
+                e += (uint32_t)(d * d);
+            }
+            if (e < best) {
+                best = e;
+                bj = j;
+            }
+        }
+        idx[i] = (uint8_t)bj;
+        total += best;
+    }
+    return total;
+}
+
+/* quantise float end points (lo, hi), choose p-bits, evaluate; keep in *out if better */
+static void quantise_and_try(const uint8_t px[16][4], int mask, const fit_cfg* cfg,
+                             const float lo[4], const float hi[4], int pb_search, fit* best) {
+    const float* xs[2] = {lo, hi};
+    int ncombo = 1;
+    int combos[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
+    if (cfg->pbmode == PB_PER_EP) {
+        if (pb_search) {
+            ncombo = 4;
+            for (int k = 0; k < 4; k++) {
+                combos[k][0] = k & 1;
+                combos[k][1] = k >> 1;
+            }
+        } else { /* per end point: the p that lands closest to the float end point */
+            for (int e = 0; e < 2; e++) {
+                float err[2];
+                for (int p = 0; p < 2; p++) {
+                    float s = 0.0f;
+                    for (int c = 0; c < cfg->nc; c++) {
+                        int q = quant_pbit(xs[e][c], cfg->bits, p);
+                        float d = (float)expand_bits((q << 1) | p, cfg->bits + 1) - xs[e][c];
+                        s = s + d * d;
+                    }
+                    err[p] = s;
+                }
+                combos[0][e] = err[1] < err[0] ? 1 : 0;
+            }
+        }
+    } else if (cfg->pbmode == PB_SHARED) {
+        if (pb_search) {
+            ncombo = 2;
+            combos[1][0] = combos[1][1] = 1;
+        } else {
+            float err[2];
+            for (int p = 0; p < 2; p++) {
+                float s = 0.0f;
+                for (int e = 0; e < 2; e++)
+                    for (int c = 0; c < cfg->nc; c++) {
+                        int q = quant_pbit(xs[e][c], cfg->bits, p);
+                        float d = (float)expand_bits((q << 1) | p, cfg->bits + 1) - xs[e][c];
+                        s = s + d * d;
+                    }
+                err[p] = s;
+            }
+            combos[0][0] = combos[0][1] = err[1] < err[0] ? 1 : 0;
+        }
+    }
+    for (int k = 0; k < ncombo; k++) {
+        fit cand;
+        memset(&cand, 0, sizeof cand);
+        for (int e = 0; e < 2; e++) {
+            cand.pbit[e] = combos[k][e];
+            for (int c = 0; c < cfg->nc; c++) {
+                if (cfg->pbmode == PB_NONE) {
+                    cand.q[e][c] = quant_plain(xs[e][c], cfg->bits);
+                    cand.e8[e][c] = expand_bits(cand.q[e][c], cfg->bits);
+                } else {
+                    cand.q[e][c] = quant_pbit(xs[e][c], cfg->bits, cand.pbit[e]);
+                    cand.e8[e][c] = expand_bits((cand.q[e][c] << 1) | cand.pbit[e], cfg->bits + 1);
+                }
+            }
+        }
+        memcpy(cand.idx, best->idx, 16);
+        cand.err = evaluate(px, mask, cfg, cand.e8, cand.idx);
+        if (cand.err < best->err) *best = cand;
+    }
+}
+
+/* Fit one subset (pixels selected by mask) with one end-point pair.  Spec v1 steps 1-6. */
+static void fit_subset(const uint8_t px[16][4], int mask, const fit_cfg* cfg, const tier* T,
+                       fit* out) {
+    const int nc = cfg->nc;
+    /* 1. integer moments */
+    int n = 0, S1[4] = {0, 0, 0, 0}, S2[4][4];
+    memset(S2, 0, sizeof S2);
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        n++;
+        for (int a = 0; a < nc; a++) {
+            int v = px[i][a];
+            S1[a] += v;
+            for (int b = a; b < nc; b++) S2[a][b] += v * px[i][b];
+        }
+    }
+    float C[4][4];
+    for (int a = 0; a < nc; a++)
+        for (int b = a; b < nc; b++) C[a][b] = C[b][a] = (float)(n * S2[a][b] - S1[a] * S1[b]);
+    /* 2. principal axis: 4 power iterations starting from the covariance column with the
+     * largest diagonal entry (all ones for a constant subset) */
+    float v[4];
+    int best = 0;
+    for (int c = 1; c < nc; c++)
+        if (C[c][c] > C[best][best]) best = c;
+    for (int c = 0; c < nc; c++) v[c] = C[best][best] > 0.0f ? C[c][best] : 1.0f;
+    for (int it = 0; it < 4; it++) {
+        float t[4], m = 0.0f;
+        for (int a = 0; a < nc; a++) {
+            float s = 0.0f;
+            for (int b = 0; b < nc; b++) s = s + C[a][b] * v[b];
+            t[a] = s;
+            float f = fabsf(s);
+            if (f > m) m = f;
+        }
+        if (m == 0.0f) break;
+        float r = 1.0f / m;
+        for (int a = 0; a < nc; a++) v[a] = t[a] * r;
+    }
+    float len2 = 0.0f;
+    for (int c = 0; c < nc; c++) len2 = len2 + v[c] * v[c];
+    float rl = 1.0f / sqrtf(len2);
+    for (int c = 0; c < nc; c++) v[c] = v[c] * rl;
+    /* 3. project, extremes along the axis */
+    float mean[4], fn = (float)n;
+    for (int c = 0; c < nc; c++) mean[c] = (float)S1[c] / fn;
+    float tmin = 3.0e38f, tmax = -3.0e38f;
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        float t = 0.0f;
+        for (int c = 0; c < nc; c++) t = t + ((float)px[i][c] - mean[c]) * v[c];
+        if (t < tmin) tmin = t;
+        if (t > tmax) tmax = t;
+    }
+    float lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
+    for (int c = 0; c < nc; c++) {
+        lo[c] = clampf(mean[c] + tmin * v[c], 0.0f, 255.0f);
+        hi[c] = clampf(mean[c] + tmax * v[c], 0.0f, 255.0f);
+    }
+    /* 4/5. quantise + evaluate */
+    memset(out, 0, sizeof *out);
+    out->err = 0xFFFFFFFFu;
+    quantise_and_try(px, mask, cfg, lo, hi, T->pb_search, out);
+    /* 6. least-squares refinement with the current indices */
+    const uint8_t* W = weights_for(cfg->ib);
+    for (int round = 0; round < T->ls_rounds; round++) {
+        int A = 0, B = 0, Cc = 0, X[4] = {0, 0, 0, 0}, Y[4] = {0, 0, 0, 0};
+        for (int i = 0; i < 16; i++) {
+            if (!((mask >> i) & 1)) continue;
+            int w = W[out->idx[i]], u = 64 - w;
+            A += u * u;
+            B += u * w;
+            Cc += w * w;
+            for (int c = 0; c < nc; c++) {
+                X[c] += u * px[i][c];
+                Y[c] += w * px[i][c];
+            }
+        }
+        float fA = (float)A, fB = (float)B, fC = (float)Cc;
+        float det = fA * fC - fB * fB;
+        if (det == 0.0f) break;
+        float k = 64.0f / det;
+        for (int c = 0; c < nc; c++) {
+            float fx = (float)X[c], fy = (float)Y[c];
+            lo[c] = clampf((fC * fx - fB * fy) * k, 0.0f, 255.0f);
+            hi[c] = clampf((fA * fy - fB * fx) * k, 0.0f, 255.0f);
+        }
+        uint32_t before = out->err;
+        quantise_and_try(px, mask, cfg, lo, hi, T->pb_search, out);
+        if (out->err >= before) break;
+    }
+}
+
+/* Partition estimator (spec v1 "estimate"): for every subset, error of the best line fit plus
+ * the index quantisation term, from integer moments.  Returns A = sum tr/n, B = sum lambda/n. */
+static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, float* tr_n,
+                              float* lam_n) {
+    /* S2 packed upper triangle: (0,0)(0,1)(0,2)(0,3)(1,1)(1,2)(1,3)(2,2)(2,3)(3,3) */
+    static const int IDX[4][4] = {{0, 1, 2, 3}, {1, 4, 5, 6}, {2, 5, 7, 8}, {3, 6, 8, 9}};
+    float C[4][4];
+    for (int a = 0; a < nc; a++)
+        for (int b = 0; b < nc; b++) C[a][b] = (float)(n * S2[IDX[a][b]] - S1[a] * S1[b]);
+    float tr = 0.0f;
+    int best = 0;
+    for (int a = 0; a < nc; a++) {
+        tr = tr + C[a][a];
+        if (C[a][a] > C[best][best]) best = a;
+    }
+    float fn = (float)n;
+    *tr_n = tr / fn;
+    *lam_n = 0.0f;
+    if (tr == 0.0f) return;
+    float v[4], w[4], m = 0.0f;
+    for (int a = 0; a < nc; a++) {
+        v[a] = C[a][best];
+        float f = fabsf(v[a]);
+        if (f > m) m = f;
+    }
+    float r = 1.0f / m;
+    for (int a = 0; a < nc; a++) v[a] = v[a] * r;
+    m = 0.0f;
+    for (int a = 0; a < nc; a++) {
+        float s = 0.0f;
+        for (int b = 0; b < nc; b++) s = s + C[a][b] * v[b];
+        w[a] = s;
+        float f = fabsf(s);
+        if (f > m) m = f;
+    }
+    if (m == 0.0f) return;
+    r = 1.0f / m;
+    for (int a = 0; a < nc; a++) w[a] = w[a] * r;
+    float wu = 0.0f, ww = 0.0f;
+    for (int a = 0; a < nc; a++) {
+        float s = 0.0f;
+        for (int b = 0; b < nc; b++) s = s + C[a][b] * w[b];
+        wu = wu + w[a] * s;
+        ww = ww + w[a] * w[a];
+    }
+    float lam = wu / ww;
+    if (lam > tr) lam = tr;
+    if (lam < 0.0f) lam = 0.0f;
+    *lam_n = lam / fn;
+}
+
+typedef struct {
+    float score[8];
+    int part[8];
+    int n;
+} toplist;
+
+static void top_insert(toplist* t, int cap, float score, int part) {
+    if (cap <= 0) return;
+    int pos = t->n;
+    while (pos > 0 && score < t->score[pos - 1]) pos--;
+    if (pos >= cap) return;
+    int last = t->n < cap ? t->n : cap - 1;
+    for (int i = last; i > pos; i--) {
+        t->score[i] = t->score[i - 1];
+        t->part[i] = t->part[i - 1];
+    }
+    t->score[pos] = score;
+    t->part[pos] = part;
+    if (t->n < cap) t->n++;
+}
+
+/* index-quantisation factor 1 - 1/(L-1)^2 for L = 2^ib palette entries */
+static float kfac(int ib) {
+    float l = (float)((1 << ib) - 1);
+    return 1.0f - 1.0f / (l * l);
+}
+
+static void pixel_moments(const uint8_t px[16][4], int i, int nc, int m1[4], int m2[10]) {
+    int k = 0;
+    for (int a = 0; a < 4; a++) {
+        m1[a] = a < nc ? px[i][a] : 0;
+        for (int b = a; b < 4; b++) m2[k++] = (a < nc && b < nc) ? px[i][a] * px[i][b] : 0;
+    }
+}
+
+/* ranks partitions for two index widths at once (ibA list, ibB list) */
+static void estimate_partitions(const uint8_t px[16][4], int ns, int nparts, int nc, int ibA,
+                                int capA, toplist* listA, int ibB, int capB, toplist* listB) {
+    int m1[16][4], m2[16][10], T1[4] = {0, 0, 0, 0}, T2[10] = {0};
+    for (int i = 0; i < 16; i++) {
+        pixel_moments(px, i, nc, m1[i], m2[i]);
+        for (int a = 0; a < 4; a++) T1[a] += m1[i][a];
+        for (int k = 0; k < 10; k++) T2[k] += m2[i][k];
+    }
+    listA->n = 0;
+    listB->n = 0;
+    const float kA = kfac(ibA), kB = kfac(ibB);
+    for (int p = 0; p < nparts; p++) {
+        int n[3] = {0, 0, 0}, S1[3][4], S2[3][10];
+        memset(S1, 0, sizeof S1);
+        memset(S2, 0, sizeof S2);
+        for (int i = 0; i < 16; i++) {
+            int s = subset_of(ns, p, i);
+            if (s == 0) continue; /* subset 0 = total - others */
+            n[s]++;
+            for (int a = 0; a < 4; a++) S1[s][a] += m1[i][a];
+            for (int k = 0; k < 10; k++) S2[s][k] += m2[i][k];
+        }
+        n[0] = 16 - n[1] - n[2];
+        for (int a = 0; a < 4; a++) S1[0][a] = T1[a] - S1[1][a] - S1[2][a];
+        for (int k = 0; k < 10; k++) S2[0][k] = T2[k] - S2[1][k] - S2[2][k];
+        float A = 0.0f, B = 0.0f;
+        for (int s = 0; s < ns; s++) {
+            float tr_n, lam_n;
+            subset_line_stats(n[s], S1[s], S2[s], nc, &tr_n, &lam_n);
+            A = A + tr_n;
+            B = B + lam_n;
+        }
+        top_insert(listA, capA, A - kA * B, p);
+        top_insert(listB, capB, A - kB * B, p);
+    }
+}
+
+typedef struct {
+    int mode, partition, rotation, idxsel;
+    int q[3][2][4];
+    int pbit[3][2];
+    uint8_t idx[16];  /* primary index set  */
+    uint8_t idx2[16]; /* secondary index set (modes 4/5) */
+    uint32_t err;
+} solution;
+
+static void try_partitioned(const uint8_t px3[16][4], const uint8_t px4[16][4], int mode,
+                            int partition, const tier* T, solution* best) {
+    const mode_info* mi = &MODES[mode];
+    fit_cfg cfg = {mi->ab ? 4 : 3, mi->cb, mi->epb ? PB_PER_EP : (mi->spb ? PB_SHARED : PB_NONE),
+                   mi->ib};
+    const uint8_t(*px)[4] = mi->ab ? px4 : px3;
+    solution s;
+    memset(&s, 0, sizeof s);
+    s.mode = mode;
+    s.partition = partition;
+    s.err = 0;
+    for (int k = 0; k < mi->ns; k++) {
+        int mask = 0;
+        for (int i = 0; i < 16; i++)
+            if (subset_of(mi->ns, partition, i) == k) mask |= 1 << i;
+        fit f;
+        fit_subset(px, mask, &cfg, T, &f);
+        for (int e = 0; e < 2; e++) {
+            s.pbit[k][e] = f.pbit[e];
+            for (int c = 0; c < 4; c++) s.q[k][e][c] = f.q[e][c];
+        }
+        for (int i = 0; i < 16; i++)
+            if ((mask >> i) & 1) s.idx[i] = f.idx[i];
+        s.err += f.err;
+        if (s.err >= best->err) return; /* cannot win any more */
+    }
+    if (s.err < best->err) *best = s;
+}
+
+static void try_mode45(const uint8_t px4[16][4], int mode, int rotation, int idxsel, const tier* T,
+                       solution* best) {
+    const mode_info* mi = &MODES[mode];
+    uint8_t col[16][4], sca[16][4];
+    for (int i = 0; i < 16; i++) {
+        uint8_t p[4] = {px4[i][0], px4[i][1], px4[i][2], px4[i][3]};
+        if (rotation) {
+            uint8_t t = p[3];
+            p[3] = p[rotation - 1];
+            p[rotation - 1] = t;
+        }
+        col[i][0] = p[0];
+        col[i][1] = p[1];
+        col[i][2] = p[2];
+        col[i][3] = 0;
+        sca[i][0] = p[3];
+        sca[i][1] = sca[i][2] = sca[i][3] = 0;
+    }
+    const int cib = idxsel ? mi->ib2 : mi->ib, aib = idxsel ? mi->ib : mi->ib2;
+    fit_cfg ccfg = {3, mi->cb, PB_NONE, cib};
+    fit_cfg acfg = {1, mi->ab, PB_NONE, aib};
+    fit fc, fa;
+    fit_subset(col, 0xFFFF, &ccfg, T, &fc);
+    if (fc.err >= best->err) return;
+    fit_subset(sca, 0xFFFF, &acfg, T, &fa);
+    uint32_t err = fc.err + fa.err;
+    if (err >= best->err) return;
+    solution s;
+    memset(&s, 0, sizeof s);
+    s.mode = mode;
+    s.rotation = rotation;
+    s.idxsel = idxsel;
+    s.err = err;
+    for (int e = 0; e < 2; e++) {
+        for (int c = 0; c < 3; c++) s.q[0][e][c] = fc.q[e][c];
+        s.q[0][e][3] = fa.q[e][0];
+    }
+    /* primary index set is the ib-bit one: colour when idxsel == 0, alpha otherwise */
+    memcpy(idxsel ? s.idx2 : s.idx, fc.idx, 16);
+    memcpy(idxsel ? s.idx : s.idx2, fa.idx, 16);
+    *best = s;
+}
+
+/* Best 7-bit end-point pair for a solid 8-bit value at index 1 of the 2-bit ramp (mode 5). */
+static uint8_t SOLID5[256][2];
+static int solid5_ready = 0;
+static void solid5_init(void) {
+    for (int c = 0; c < 256; c++) {
+        int best = 1 << 30, bl = 0, bh = 0;
+        for (int l = 0; l < 128; l++)
+            for (int h = 0; h < 128; h++) {
+                int v = interp(expand_bits(l, 7), expand_bits(h, 7), 21);
+                int e = (v - c) * (v - c) * 256 + (l > h ? l - h : h - l); /* exactness, then span */
+                if (e < best) {
+                    best = e;
+                    bl = l;
+                    bh = h;
+                }
+            }
+        SOLID5[c][0] = (uint8_t)bl;
+        SOLID5[c][1] = (uint8_t)bh;
+    }
+    solid5_ready = 1;
+}
+
+typedef struct {
+    uint8_t* d;
+    int pos;
+} bitwriter;
+
+static void wr(bitwriter* w, int v, int n) {
+    for (int i = 0; i < n; i++, w->pos++)
+        if ((v >> i) & 1) w->d[w->pos >> 3] |= (uint8_t)(1 << (w->pos & 7));
+}
+
+static void pack_solution(solution* s, uint8_t blk[16]) {
+    const mode_info* mi = &MODES[s->mode];
+    int anchor[3];
+    anchors_of(mi->ns, s->partition, anchor);
+    /* anchor rule: the anchor texel's index must have a clear MSB; swap end points if not */
+    for (int k = 0; k < mi->ns; k++) {
+        if (s->idx[anchor[k]] >> (mi->ib - 1)) {
+            const int maxi = (1 << mi->ib) - 1;
+            for (int i = 0; i < 16; i++)
+                if (subset_of(mi->ns, s->partition, i) == k) s->idx[i] = (uint8_t)(maxi - s->idx[i]);
+            if (mi->ib2 == 0) { /* one index set drives all channels */
+                for (int c = 0; c < 4; c++) {
+                    int t = s->q[k][0][c];
+                    s->q[k][0][c] = s->q[k][1][c];
+                    s->q[k][1][c] = t;
+                }
+                int t = s->pbit[k][0];
+                s->pbit[k][0] = s->pbit[k][1];
+                s->pbit[k][1] = t;
+            } else { /* modes 4/5: primary set = colour (idxsel 0) or alpha (idxsel 1) */
+                int c0 = s->idxsel ? 3 : 0, c1 = s->idxsel ? 4 : 3;
+                for (int c = c0; c < c1; c++) {
+                    int t = s->q[k][0][c];
+                    s->q[k][0][c] = s->q[k][1][c];
+                    s->q[k][1][c] = t;
+                }
+            }
+        }
+    }
+    if (mi->ib2 && (s->idx2[0] >> (mi->ib2 - 1))) {
+        const int maxi = (1 << mi->ib2) - 1;
+        for (int i = 0; i < 16; i++) s->idx2[i] = (uint8_t)(maxi - s->idx2[i]);
+        int c0 = s->idxsel ? 0 : 3, c1 = s->idxsel ? 3 : 4;
+        for (int c = c0; c < c1; c++) {
+            int t = s->q[0][0][c];
+            s->q[0][0][c] = s->q[0][1][c];
+            s->q[0][1][c] = t;
+        }
+    }
+    memset(blk, 0, 16);
+    bitwriter w = {blk, 0};
+    wr(&w, 1 << s->mode, s->mode + 1);
+    wr(&w, s->partition, mi->pb);
+    wr(&w, s->rotation, mi->rb);
+    wr(&w, s->idxsel, mi->isb);
+    for (int c = 0; c < 3; c++)
+        for (int k = 0; k < mi->ns; k++)
+            for (int e = 0; e < 2; e++) wr(&w, s->q[k][e][c], mi->cb);
+    if (mi->ab)
+        for (int k = 0; k < mi->ns; k++)
+            for (int e = 0; e < 2; e++) wr(&w, s->q[k][e][3], mi->ab);
+    if (mi->epb)
+        for (int k = 0; k < mi->ns; k++)
+            for (int e = 0; e < 2; e++) wr(&w, s->pbit[k][e], 1);
+    if (mi->spb)
+        for (int k = 0; k < mi->ns; k++) wr(&w, s->pbit[k][0], 1);
+    for (int i = 0; i < 16; i++) {
+        int is_anchor = (i == anchor[0]) || (i == anchor[1]) || (i == anchor[2]);
+        wr(&w, s->idx[i], mi->ib - is_anchor);
+    }
+    if (mi->ib2)
+        for (int i = 0; i < 16; i++) wr(&w, s->idx2[i], mi->ib2 - (i == 0));
+}
+
+void oracle_bc7_encode_block(const uint8_t rgba[64], int quality, uint8_t blk[16]) {
+    const tier* T = &TIERS[quality < 0 ? 0 : (quality > 2 ? 2 : quality)];
+    uint8_t px4[16][4], px3[16][4];
+    int solid = 1, has_alpha = 0;
+    for (int i = 0; i < 16; i++) {
+        for (int c = 0; c < 4; c++) px4[i][c] = rgba[4 * i + c];
+        px3[i][0] = px4[i][0];
+        px3[i][1] = px4[i][1];
+        px3[i][2] = px4[i][2];
+        px3[i][3] = 0;
+        if (memcmp(px4[i], px4[0], 4)) solid = 0;
+        if (px4[i][3] != 255) has_alpha = 1;
+    }
+    solution best;
+    memset(&best, 0, sizeof best);
+    best.err = 0xFFFFFFFFu;
+    if (solid) { /* exact (or nearest) single colour: mode 5, rotation 0, colour index 1 */
+        if (!solid5_ready) solid5_init();
+        best.mode = 5;
+        for (int c = 0; c < 3; c++) {
+            best.q[0][0][c] = SOLID5[px4[0][c]][0];
+            best.q[0][1][c] = SOLID5[px4[0][c]][1];
+        }
+        best.q[0][0][3] = best.q[0][1][3] = px4[0][3];
+        for (int i = 0; i < 16; i++) {
+            best.idx[i] = 1;
+            best.idx2[i] = 0;
+        }
+        pack_solution(&best, blk);
+        return;
+    }
+    /* mode 6: one subset, RGBA 7.7.7.7 + p-bit per end point, 4-bit indices */
+    try_partitioned(px3, px4, 6, 0, T, &best);
+    if (!has_alpha) {
+        toplist l1, l3;
+        estimate_partitions(px4, 2, 64, 3, 3, T->n1, &l1, 2, T->n3, &l3);
+        for (int i = 0; i < l1.n; i++) try_partitioned(px3, px4, 1, l1.part[i], T, &best);
+        for (int i = 0; i < l3.n; i++) try_partitioned(px3, px4, 3, l3.part[i], T, &best);
+        if (T->n0 || T->n2) {
+            toplist l0, l2, dummy;
+            estimate_partitions(px4, 3, 16, 3, 3, T->n0, &l0, 2, 0, &dummy);
+            estimate_partitions(px4, 3, 64, 3, 2, T->n2, &l2, 2, 0, &dummy);
+            for (int i = 0; i < l0.n; i++) try_partitioned(px3, px4, 0, l0.part[i], T, &best);
+            for (int i = 0; i < l2.n; i++) try_partitioned(px3, px4, 2, l2.part[i], T, &best);
+        }
+    } else {
+        toplist l7, dummy;
+        estimate_partitions(px4, 2, 64, 4, 2, T->n7, &l7, 2, 0, &dummy);
+        for (int i = 0; i < l7.n; i++) try_partitioned(px3, px4, 7, l7.part[i], T, &best);
+    }
+    for (int r = 0; r < T->rot5; r++) try_mode45(px4, 5, r, 0, T, &best);
+    for (int r = 0; r < T->rot4; r++) {
+        try_mode45(px4, 4, r, 0, T, &best);
+        try_mode45(px4, 4, r, 1, T, &best);
+    }
+    pack_solution(&best, blk);
+}
+
+/* ------------------------------------------------------------------ images */
+
+static void gather_block(const uint8_t* rgba, int w, int h, int bx, int by, uint8_t out[64]) {
+    for (int y = 0; y < 4; y++) {
+        int sy = 4 * by + y;
+        if (sy > h - 1) sy = h - 1; /* partial blocks: repeat the edge texels (row A9) */
+        for (int x = 0; x < 4; x++) {
+            int sx = 4 * bx + x;
+            if (sx > w - 1) sx = w - 1;
+            memcpy(out + 4 * (4 * y + x), rgba + 4 * ((size_t)sy * w + sx), 4);
+        }
+    }
+}
+
+#include <pthread.h>
+#include <stdatomic.h>
+#include <unistd.h>
+
+int oracle_max_threads(void) {
+    long n = sysconf(_SC_NPROCESSORS_ONLN);
+    return n < 1 ? 1 : (int)n;
+}
+
+typedef struct {
+    const uint8_t* rgba;
+    int w, h, fmt, quality;
+    uint8_t* blocks;
+    atomic_int next;
+} encode_job;
+
+#define ENCODE_CHUNK 64
+
+static void* encode_worker(void* arg) {
+    encode_job* j = (encode_job*)arg;
+    const int bw = (j->w + 3) / 4, bh = (j->h + 3) / 4;
+    const int bb = j->fmt == ORACLE_FMT_BC4 ? 8 : 16;
+    for (;;) {
+        int b0 = atomic_fetch_add(&j->next, ENCODE_CHUNK);
+        if (b0 >= bw * bh) break;
+        int b1 = b0 + ENCODE_CHUNK < bw * bh ? b0 + ENCODE_CHUNK : bw * bh;
+        for (int b = b0; b < b1; b++) {
+            uint8_t px[64];
+            gather_block(j->rgba, j->w, j->h, b % bw, b / bw, px);
+            uint8_t* dst = j->blocks + (size_t)b * bb;
+            if (j->fmt == ORACLE_FMT_BC7) {
+                oracle_bc7_encode_block(px, j->quality, dst);
+            } else if (j->fmt == ORACLE_FMT_BC5) {
+                uint8_t rg[32];
+                for (int i = 0; i < 16; i++) {
+                    rg[2 * i] = px[4 * i];
+                    rg[2 * i + 1] = px[4 * i + 1];
+                }
+                oracle_bc5_encode_block(rg, dst);
+            } else {
+                uint8_t r[16];
+                for (int i = 0; i < 16; i++) r[i] = px[4 * i];
+                oracle_bc4_encode_block(r, dst);
+            }
+        }
+    }
+    return NULL;
+}
+
+/* Context::compress over one level (row A9): blocks row-major, work shared by `threads`
+ * host threads (<= 0: all cores) */
+void oracle_encode_image(const uint8_t* rgba, int w, int h, int fmt, int quality, uint8_t* blocks,
+                         int threads) {
+    if (!solid5_ready) solid5_init();
+    encode_job job = {rgba, w, h, fmt, quality, blocks, 0};
+    const int nblocks = ((w + 3) / 4) * ((h + 3) / 4);
+    if (threads <= 0) threads = oracle_max_threads();
+    if (threads > (nblocks + ENCODE_CHUNK - 1) / ENCODE_CHUNK)
+        threads = (nblocks + ENCODE_CHUNK - 1) / ENCODE_CHUNK;
+    if (threads <= 1) {
+        encode_worker(&job);
+        return;
+    }
+    pthread_t tid[256];
+    if (threads > 256) threads = 256;
+    for (int t = 1; t < threads; t++) pthread_create(&tid[t], NULL, encode_worker, &job);
+    encode_worker(&job);
+    for (int t = 1; t < threads; t++) pthread_join(tid[t], NULL);
+}
+
+void oracle_decode_image(const uint8_t* blocks, int w, int h, int fmt, uint8_t* rgba) {
+    const int bw = (w + 3) / 4, bh = (h + 3) / 4;
+    const int bb = fmt == ORACLE_FMT_BC4 ? 8 : 16;
+    for (int b = 0; b < bw * bh; b++) {
+        uint8_t px[64];
+        const uint8_t* src = blocks + (size_t)b * bb;
+        if (fmt == ORACLE_FMT_BC7) {
+            oracle_bc7_decode_block(src, px);
+        } else {
+            uint8_t r[16], g[16];
+            memset(g, 0, 16);
+            oracle_bc4_decode_block(src, r);
+            if (fmt == ORACLE_FMT_BC5) oracle_bc4_decode_block(src + 8, g);
+            for (int i = 0; i < 16; i++) {
+                px[4 * i] = r[i];
+                px[4 * i + 1] = g[i];
+                px[4 * i + 2] = 0;
+                px[4 * i + 3] = 255;
+            }
+        }
+        int bx = b % bw, by = b / bw;
+        for (int y = 0; y < 4 && 4 * by + y < h; y++)
+            for (int x = 0; x < 4 && 4 * bx + x < w; x++)
+                memcpy(rgba + 4 * ((size_t)(4 * by + y) * w + 4 * bx + x), px + 4 * (4 * y + x), 4);
+    }
+}
+
+/* generate_srgb_texture / generate_normal_map_texture, Packager.cpp:216-308, memory to memory */
+#include <stdlib.h>
+size_t oracle_generate_texture(const uint8_t* rgba, int w, int h, int kind, int fmt, int quality,
+                               int normalize_mode, uint8_t* dds_out, int threads) {
+    const int levels = oracle_count_mipmaps(w, h);
+    uint8_t* chain = (uint8_t*)malloc(4 * oracle_chain_pixels(w, h));
+    if (kind == ORACLE_KIND_NORMAL)
+        oracle_mip_chain_normal(rgba, w, h, normalize_mode, chain);
+    else
+        oracle_mip_chain_srgb(rgba, w, h, chain);
+    oracle_dds_header(w, h, levels, fmt, dds_out); /* :237 / :286 */
+    uint8_t* dst = dds_out + ORACLE_DDS_HEADER_BYTES;
+    const uint8_t* src = chain;
+    const int bb = fmt == ORACLE_FMT_BC4 ? 8 : 16;
+    for (int l = 0; l < levels; l++) { /* :243-259 / :292-306: levels appended largest first */
+        int lw, lh;
+        oracle_level_extent(w, h, l, &lw, &lh);
+        oracle_encode_image(src, lw, lh, fmt, quality, dst, threads);
+        dst += (size_t)((lw + 3) / 4) * ((lh + 3) / 4) * bb;
+        src += (size_t)4 * lw * lh;
+    }
+    free(chain);
+    return (size_t)(dst - dds_out);
+}
