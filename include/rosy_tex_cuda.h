@@ -123,6 +123,13 @@ ROSY_TEX_API int rosy_tex_generate_normal_map_texture(const char* image_path);
 ROSY_TEX_API int rosy_tex_generate_texture_file(const char* image_path, int kind,
                                                 const char* dds_path);
 
+/* nvtt::Surface::load stand-in (Packager.cpp:222, :269), exposed so the decoder can be tested on
+ * its own: decodes PNG / TGA / PNM / .rgba8 into a malloc'd RGBA8 buffer (free with
+ * rosy_tex_free_image).  Host only; needs no device. */
+ROSY_TEX_API int rosy_tex_load_image(const char* image_path, uint8_t** rgba, uint32_t* width,
+                                     uint32_t* height);
+ROSY_TEX_API void rosy_tex_free_image(uint8_t* rgba);
+
 /* ---- geometry helpers (nvtt::Surface::countMipmaps, Packager.cpp:235; dds.hpp:527-565) ---- */
 ROSY_TEX_API int rosy_tex_count_mipmaps(uint32_t width, uint32_t height);
 ROSY_TEX_API void rosy_tex_level_extent(uint32_t width, uint32_t height, int level, uint32_t* w,
@@ -164,7 +171,8 @@ ROSY_TEX_API void rosy_tex_free_host(void* p);
  * (NULL: legacy default stream).  Nothing synchronises; kernels are only enqueued.
  *   d_chain  : rosy_tex_chain_size() bytes.  Receives levels 1.. (and level 0 for normal maps,
  *              whose level 0 is re-normalised); for colour maps level 0 is read from d_rgba.
- *   d_scratch: rosy_tex_device_scratch_size() bytes.
+ *   d_scratch: rosy_tex_device_scratch_size() bytes; its first 256 bytes must be zero before the
+ *              first use (the kernels leave them zero again).
  *   d_blocks : rosy_tex_dds_size() - 148 bytes, every level's blocks, largest level first. */
 ROSY_TEX_API size_t rosy_tex_device_scratch_size(const rosy_tex_desc* desc);
 ROSY_TEX_API int rosy_tex_mips_device(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain,

@@ -454,25 +454,28 @@ static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, 
     *lam_n = lam / fn;
 }
 
+/* Best-first list of partitions.  Entries are ordered by the key
+ *   (bits of the non-negative fp32 score with the low 6 mantissa bits replaced by the partition)
+ * so that one unsigned compare orders by (truncated score, partition). */
+#define TOPK 6
 typedef struct {
-    float score[8];
-    int part[8];
-    int n;
+    uint32_t key[TOPK];
 } toplist;
 
-static void top_insert(toplist* t, int cap, float score, int part) {
-    if (cap <= 0) return;
-    int pos = t->n;
-    while (pos > 0 && score < t->score[pos - 1]) pos--;
-    if (pos >= cap) return;
-    int last = t->n < cap ? t->n : cap - 1;
-    for (int i = last; i > pos; i--) {
-        t->score[i] = t->score[i - 1];
-        t->part[i] = t->part[i - 1];
+static void top_init(toplist* t) {
+    for (int k = 0; k < TOPK; k++) t->key[k] = 0xFFFFFFFFu;
+}
+
+static void top_insert(toplist* t, float score, int part) {
+    if (score < 0.0f) score = 0.0f;
+    uint32_t bits;
+    memcpy(&bits, &score, 4);
+    uint32_t key = (bits & ~63u) | (uint32_t)part;
+    for (int k = 0; k < TOPK; k++) {
+        uint32_t lo = t->key[k] < key ? t->key[k] : key;
+        key = t->key[k] < key ? key : t->key[k];
+        t->key[k] = lo;
     }
-    t->score[pos] = score;
-    t->part[pos] = part;
-    if (t->n < cap) t->n++;
 }
 
 /* index-quantisation factor 1 - 1/(L-1)^2 for L = 2^ib palette entries */
@@ -491,15 +494,15 @@ static void pixel_moments(const uint8_t px[16][4], int i, int nc, int m1[4], int
 
 /* ranks partitions for two index widths at once (ibA list, ibB list) */
 static void estimate_partitions(const uint8_t px[16][4], int ns, int nparts, int nc, int ibA,
-                                int capA, toplist* listA, int ibB, int capB, toplist* listB) {
+                                toplist* listA, int ibB, toplist* listB) {
     int m1[16][4], m2[16][10], T1[4] = {0, 0, 0, 0}, T2[10] = {0};
     for (int i = 0; i < 16; i++) {
         pixel_moments(px, i, nc, m1[i], m2[i]);
         for (int a = 0; a < 4; a++) T1[a] += m1[i][a];
         for (int k = 0; k < 10; k++) T2[k] += m2[i][k];
     }
-    listA->n = 0;
-    listB->n = 0;
+    top_init(listA);
+    top_init(listB);
     const float kA = kfac(ibA), kB = kfac(ibB);
     for (int p = 0; p < nparts; p++) {
         int n[3] = {0, 0, 0}, S1[3][4], S2[3][10];
@@ -522,8 +525,8 @@ static void estimate_partitions(const uint8_t px[16][4], int ns, int nparts, int
             A = A + tr_n;
             B = B + lam_n;
         }
-        top_insert(listA, capA, A - kA * B, p);
-        top_insert(listB, capB, A - kB * B, p);
+        top_insert(listA, A - kA * B, p);
+        top_insert(listB, A - kB * B, p);
     }
 }
 
@@ -738,21 +741,23 @@ void oracle_bc7_encode_block(const uint8_t rgba[64], int quality, uint8_t blk[16
     /* mode 6: one subset, RGBA 7.7.7.7 + p-bit per end point, 4-bit indices */
     try_partitioned(px3, px4, 6, 0, T, &best);
     if (!has_alpha) {
-        toplist l1, l3;
-        estimate_partitions(px4, 2, 64, 3, 3, T->n1, &l1, 2, T->n3, &l3);
-        for (int i = 0; i < l1.n; i++) try_partitioned(px3, px4, 1, l1.part[i], T, &best);
-        for (int i = 0; i < l3.n; i++) try_partitioned(px3, px4, 3, l3.part[i], T, &best);
+        if (T->n1 || T->n3) {
+            toplist l1, l3;
+            estimate_partitions(px4, 2, 64, 3, 3, &l1, 2, &l3);
+            for (int i = 0; i < T->n1; i++) try_partitioned(px3, px4, 1, l1.key[i] & 63, T, &best);
+            for (int i = 0; i < T->n3; i++) try_partitioned(px3, px4, 3, l3.key[i] & 63, T, &best);
+        }
         if (T->n0 || T->n2) {
             toplist l0, l2, dummy;
-            estimate_partitions(px4, 3, 16, 3, 3, T->n0, &l0, 2, 0, &dummy);
-            estimate_partitions(px4, 3, 64, 3, 2, T->n2, &l2, 2, 0, &dummy);
-            for (int i = 0; i < l0.n; i++) try_partitioned(px3, px4, 0, l0.part[i], T, &best);
-            for (int i = 0; i < l2.n; i++) try_partitioned(px3, px4, 2, l2.part[i], T, &best);
+            estimate_partitions(px4, 3, 16, 3, 3, &l0, 2, &dummy);
+            estimate_partitions(px4, 3, 64, 3, 2, &l2, 2, &dummy);
+            for (int i = 0; i < T->n0; i++) try_partitioned(px3, px4, 0, l0.key[i] & 63, T, &best);
+            for (int i = 0; i < T->n2; i++) try_partitioned(px3, px4, 2, l2.key[i] & 63, T, &best);
         }
-    } else {
+    } else if (T->n7) {
         toplist l7, dummy;
-        estimate_partitions(px4, 2, 64, 4, 2, T->n7, &l7, 2, 0, &dummy);
-        for (int i = 0; i < l7.n; i++) try_partitioned(px3, px4, 7, l7.part[i], T, &best);
+        estimate_partitions(px4, 2, 64, 4, 2, &l7, 2, &dummy);
+        for (int i = 0; i < T->n7; i++) try_partitioned(px3, px4, 7, l7.key[i] & 63, T, &best);
     }
     for (int r = 0; r < T->rot5; r++) try_mode45(px4, 5, r, 0, T, &best);
     for (int r = 0; r < T->rot4; r++) {

@@ -1,0 +1,356 @@
+// image_io.cpp - host-side image file decode for the path entry points.
+//
+// Stands in for nvtt::Surface::load (/root/reference/src/Packager/Packager.cpp:222, :269; SURVEY
+// row A3): decode a file to 8-bit RGBA, images without alpha get alpha = 255.  glTF image URIs
+// (src/Packager/Gltf.cpp:98-111) are PNG / JPEG; the FBX path feeds TGA (src/Packager/Fbx.cpp:421-438).
+// Written from the PNG / TGA / PNM specifications (zlib does the inflate); JPEG is not decoded yet
+//  and reports ROSY_TEX_ERR_DECODE.  Raw ".rgba8" files (u32 width, u32 height,
+// pixels) are accepted for benchmarks.
+#include <ctype.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <zlib.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/rosy_tex_cuda.h"
+
+namespace rosy_tex {
+
+static bool read_file(const char* path, std::vector<uint8_t>& out) {
+    FILE* f = fopen(path, "rb");
+    if (!f) return false;
+    fseek(f, 0, SEEK_END);
+    long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    if (n < 0) {
+        fclose(f);
+        return false;
+    }
+    out.resize((size_t)n);
+    size_t got = n ? fread(out.data(), 1, (size_t)n, f) : 0;
+    fclose(f);
+    return got == (size_t)n;
+}
+
+static uint32_t be32(const uint8_t* p) {
+    return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+}
+
+// ---------------------------------------------------------------- PNG
+static int paeth(int a, int b, int c) {
+    int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+// undo the scanline filters of one (sub)image in place; returns false on a bad filter byte
+static bool png_unfilter(uint8_t* data, size_t w, size_t h, int bpp_bits) {
+    const size_t stride = (w * (size_t)bpp_bits + 7) / 8, bpp = (size_t)(bpp_bits + 7) / 8;
+    std::vector<uint8_t> zero(stride, 0);
+    const uint8_t* prev = zero.data();
+    for (size_t y = 0; y < h; y++) {
+        uint8_t* row = data + y * (stride + 1);
+        const int ft = row[0];
+        uint8_t* cur = row + 1;
+        for (size_t i = 0; i < stride; i++) {
+            const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+            int v = cur[i];
+            switch (ft) {
+                case 0: break;
+                case 1: v += a; break;
+                case 2: v += b; break;
+                case 3: v += (a + b) >> 1; break;
+                case 4: v += paeth(a, b, c); break;
+                default: return false;
+            }
+            cur[i] = (uint8_t)v;
+        }
+        prev = cur;
+    }
+    return true;
+}
+
+static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H) {
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    if (f.size() < 8 + 25 || memcmp(f.data(), sig, 8)) return ROSY_TEX_ERR_DECODE;
+    size_t pos = 8;
+    uint32_t w = 0, h = 0;
+    int depth = 0, ctype = 0, interlace = 0;
+    std::vector<uint8_t> idat, plte, trns;
+    bool have_ihdr = false, done = false;
+    while (!done && pos + 12 <= f.size()) {
+        const uint32_t len = be32(&f[pos]);
+        const uint8_t* type = &f[pos + 4];
+        const uint8_t* body = &f[pos + 8];
+        if (pos + 12 + (size_t)len > f.size()) return ROSY_TEX_ERR_DECODE;
+        if (!memcmp(type, "IHDR", 4)) {
+            if (len < 13) return ROSY_TEX_ERR_DECODE;
+            w = be32(body);
+            h = be32(body + 4);
+            depth = body[8];
+            ctype = body[9];
+            interlace = body[12];
+            if (body[10] != 0 || body[11] != 0 || interlace > 1) return ROSY_TEX_ERR_DECODE;
+            have_ihdr = true;
+        } else if (!memcmp(type, "PLTE", 4)) {
+            plte.assign(body, body + len);
+        } else if (!memcmp(type, "tRNS", 4)) {
+            trns.assign(body, body + len);
+        } else if (!memcmp(type, "IDAT", 4)) {
+            idat.insert(idat.end(), body, body + len);
+        } else if (!memcmp(type, "IEND", 4)) {
+            done = true;
+        }
+        pos += 12 + (size_t)len;
+    }
+    if (!have_ihdr || w == 0 || h == 0 || w > (1u << 15) || h > (1u << 15)) return ROSY_TEX_ERR_DECODE;
+    int channels;
+    switch (ctype) {
+        case 0: channels = 1; break;
+        case 2: channels = 3; break;
+        case 3: channels = 1; break;
+        case 4: channels = 2; break;
+        case 6: channels = 4; break;
+        default: return ROSY_TEX_ERR_DECODE;
+    }
+    if (!(depth == 1 || depth == 2 || depth == 4 || depth == 8 || depth == 16)) return ROSY_TEX_ERR_DECODE;
+    if ((ctype == 2 || ctype == 4 || ctype == 6) && depth < 8) return ROSY_TEX_ERR_DECODE;
+    if (ctype == 3 && (depth == 16 || plte.empty())) return ROSY_TEX_ERR_DECODE;
+    const int bpp_bits = channels * depth;
+    // passes: {x0, y0, dx, dy}
+    static const int adam7[7][4] = {{0, 0, 8, 8}, {4, 0, 8, 8}, {0, 4, 4, 8}, {2, 0, 4, 4},
+                                    {0, 2, 2, 4}, {1, 0, 2, 2}, {0, 1, 1, 2}};
+    const int npass = interlace ? 7 : 1;
+    size_t raw_size = 0;
+    for (int p = 0; p < npass; p++) {
+        const size_t pw = interlace ? (w - adam7[p][0] + adam7[p][2] - 1) / adam7[p][2] : w;
+        const size_t ph = interlace ? (h - adam7[p][1] + adam7[p][3] - 1) / adam7[p][3] : h;
+        if (interlace && (w <= (uint32_t)adam7[p][0] || h <= (uint32_t)adam7[p][1])) continue;
+        if (pw && ph) raw_size += ph * (1 + (pw * (size_t)bpp_bits + 7) / 8);
+    }
+    std::vector<uint8_t> raw(raw_size);
+    uLongf got = (uLongf)raw_size;
+    const int zr = uncompress(raw.data(), &got, idat.data(), (uLong)idat.size());
+    if ((zr != Z_OK && zr != Z_BUF_ERROR) || got != raw_size) return ROSY_TEX_ERR_DECODE;
+    W = w;
+    H = h;
+    rgba.assign((size_t)w * h * 4, 255);
+    size_t off = 0;
+    const int maxv = (1 << (depth > 8 ? 8 : depth)) - 1;
+    for (int p = 0; p < npass; p++) {
+        size_t pw = w, ph = h;
+        int x0 = 0, y0 = 0, dx = 1, dy = 1;
+        if (interlace) {
+            x0 = adam7[p][0];
+            y0 = adam7[p][1];
+            dx = adam7[p][2];
+            dy = adam7[p][3];
+            if (w <= (uint32_t)x0 || h <= (uint32_t)y0) continue;
+            pw = (w - x0 + dx - 1) / dx;
+            ph = (h - y0 + dy - 1) / dy;
+        }
+        if (!pw || !ph) continue;
+        const size_t stride = (pw * (size_t)bpp_bits + 7) / 8;
+        uint8_t* sub = raw.data() + off;
+        if (!png_unfilter(sub, pw, ph, bpp_bits)) return ROSY_TEX_ERR_DECODE;
+        for (size_t y = 0; y < ph; y++) {
+            const uint8_t* row = sub + y * (stride + 1) + 1;
+            for (size_t x = 0; x < pw; x++) {
+                int s[4] = {0, 0, 0, 0};   // samples as 8-bit (16-bit: high byte, like stb_image)
+                int s16[4] = {0, 0, 0, 0};  // full samples for the tRNS colour key
+                for (int c = 0; c < channels; c++) {
+                    if (depth == 16) {
+                        s16[c] = (row[(x * channels + c) * 2] << 8) | row[(x * channels + c) * 2 + 1];
+                        s[c] = s16[c] >> 8;
+                    } else if (depth == 8) {
+                        s16[c] = s[c] = row[x * channels + c];
+                    } else {
+                        const size_t bit = x * (size_t)depth;
+                        s16[c] = s[c] = (row[bit >> 3] >> (8 - depth - (bit & 7))) & maxv;
+                    }
+                }
+                uint8_t* o = &rgba[(((size_t)y0 + y * dy) * w + x0 + x * dx) * 4];
+                switch (ctype) {
+                    case 0: {
+                        const int g = depth < 8 ? s[0] * 255 / maxv : s[0];
+                        o[0] = o[1] = o[2] = (uint8_t)g;
+                        o[3] = (trns.size() >= 2 && s16[0] == ((trns[0] << 8) | trns[1])) ? 0 : 255;
+                        break;
+                    }
+                    case 2:
+                        o[0] = (uint8_t)s[0];
+                        o[1] = (uint8_t)s[1];
+                        o[2] = (uint8_t)s[2];
+                        o[3] = (trns.size() >= 6 && s16[0] == ((trns[0] << 8) | trns[1]) &&
+                                s16[1] == ((trns[2] << 8) | trns[3]) && s16[2] == ((trns[4] << 8) | trns[5]))
+                                   ? 0
+                                   : 255;
+                        break;
+                    case 3: {
+                        const size_t k = (size_t)s[0];
+                        if (3 * k + 2 >= plte.size()) return ROSY_TEX_ERR_DECODE;
+                        o[0] = plte[3 * k];
+                        o[1] = plte[3 * k + 1];
+                        o[2] = plte[3 * k + 2];
+                        o[3] = k < trns.size() ? trns[k] : 255;
+                        break;
+                    }
+                    case 4:
+                        o[0] = o[1] = o[2] = (uint8_t)s[0];
+                        o[3] = (uint8_t)s[1];
+                        break;
+                    default:
+                        o[0] = (uint8_t)s[0];
+                        o[1] = (uint8_t)s[1];
+                        o[2] = (uint8_t)s[2];
+                        o[3] = (uint8_t)s[3];
+                }
+            }
+        }
+        off += ph * (stride + 1);
+    }
+    return ROSY_TEX_OK;
+}
+
+// ---------------------------------------------------------------- TGA (types 2, 3, 10, 11; 8/24/32 bpp)
+static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H) {
+    if (f.size() < 18) return ROSY_TEX_ERR_DECODE;
+    const int idlen = f[0], cmap = f[1], type = f[2];
+    const uint32_t w = f[12] | (f[13] << 8), h = f[14] | (f[15] << 8);
+    const int bpp = f[16], desc = f[17];
+    if (cmap != 0 || !(type == 2 || type == 3 || type == 10 || type == 11)) return ROSY_TEX_ERR_DECODE;
+    const bool grey = type == 3 || type == 11, rle = type >= 10;
+    if (!((grey && bpp == 8) || (!grey && (bpp == 24 || bpp == 32))) || w == 0 || h == 0) return ROSY_TEX_ERR_DECODE;
+    const size_t bytes = (size_t)bpp / 8, n = (size_t)w * h;
+    std::vector<uint8_t> px(n * bytes);
+    size_t pos = 18 + (size_t)idlen;
+    if (!rle) {
+        if (pos + n * bytes > f.size()) return ROSY_TEX_ERR_DECODE;
+        memcpy(px.data(), &f[pos], n * bytes);
+    } else {
+        size_t o = 0;
+        while (o < n) {
+            if (pos >= f.size()) return ROSY_TEX_ERR_DECODE;
+            const int hd = f[pos++];
+            const size_t cnt = (size_t)(hd & 127) + 1;
+            if (o + cnt > n) return ROSY_TEX_ERR_DECODE;
+            if (hd & 128) {
+                if (pos + bytes > f.size()) return ROSY_TEX_ERR_DECODE;
+                for (size_t k = 0; k < cnt; k++) memcpy(&px[(o + k) * bytes], &f[pos], bytes);
+                pos += bytes;
+            } else {
+                if (pos + cnt * bytes > f.size()) return ROSY_TEX_ERR_DECODE;
+                memcpy(&px[o * bytes], &f[pos], cnt * bytes);
+                pos += cnt * bytes;
+            }
+            o += cnt;
+        }
+    }
+    W = w;
+    H = h;
+    rgba.resize(n * 4);
+    const bool top = desc & 0x20, right = desc & 0x10;
+    for (uint32_t y = 0; y < h; y++)
+        for (uint32_t x = 0; x < w; x++) {
+            const size_t sy = top ? y : h - 1 - y, sx = right ? w - 1 - x : x;
+            const uint8_t* s = &px[(sy * w + sx) * bytes];
+            uint8_t* o = &rgba[((size_t)y * w + x) * 4];
+            if (grey) {
+                o[0] = o[1] = o[2] = s[0];
+                o[3] = 255;
+            } else {
+                o[0] = s[2];
+                o[1] = s[1];
+                o[2] = s[0];
+                o[3] = bytes == 4 ? s[3] : 255;
+            }
+        }
+    return ROSY_TEX_OK;
+}
+
+// ---------------------------------------------------------------- binary PNM (P5 / P6, maxval 255)
+static int decode_pnm(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H) {
+    size_t pos = 2;
+    uint32_t vals[3];
+    for (int k = 0; k < 3; k++) {
+        for (;;) {
+            while (pos < f.size() && (f[pos] == ' ' || f[pos] == '\n' || f[pos] == '\r' || f[pos] == '\t')) pos++;
+            if (pos < f.size() && f[pos] == '#')
+                while (pos < f.size() && f[pos] != '\n') pos++;
+            else
+                break;
+        }
+        uint32_t v = 0;
+        bool any = false;
+        while (pos < f.size() && f[pos] >= '0' && f[pos] <= '9') {
+            v = v * 10 + (uint32_t)(f[pos++] - '0');
+            any = true;
+        }
+        if (!any) return ROSY_TEX_ERR_DECODE;
+        vals[k] = v;
+    }
+    pos++;  // single whitespace after maxval
+    const int ch = f[1] == '6' ? 3 : 1;
+    const size_t n = (size_t)vals[0] * vals[1];
+    if (vals[2] != 255 || n == 0 || pos + n * ch > f.size()) return ROSY_TEX_ERR_DECODE;
+    W = vals[0];
+    H = vals[1];
+    rgba.resize(n * 4);
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t* s = &f[pos + i * ch];
+        rgba[4 * i] = s[0];
+        rgba[4 * i + 1] = ch == 3 ? s[1] : s[0];
+        rgba[4 * i + 2] = ch == 3 ? s[2] : s[0];
+        rgba[4 * i + 3] = 255;
+    }
+    return ROSY_TEX_OK;
+}
+
+int decode_image_memory(const uint8_t* data, size_t len, const char* name_hint, std::vector<uint8_t>& rgba,
+                        uint32_t& w, uint32_t& h, std::string& err) {
+    std::vector<uint8_t> f(data, data + len);
+    int rc = ROSY_TEX_ERR_DECODE;
+    const std::string name = name_hint ? name_hint : "";
+    auto ends_with = [&](const char* ext) {
+        const size_t n = strlen(ext);
+        if (name.size() < n) return false;
+        for (size_t i = 0; i < n; i++)
+            if (tolower((unsigned char)name[name.size() - n + i]) != ext[i]) return false;
+        return true;
+    };
+    if (len >= 8 && f[0] == 0x89 && f[1] == 'P') {
+        rc = decode_png(f, rgba, w, h);
+    } else if (len >= 2 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) {
+        rc = decode_pnm(f, rgba, w, h);
+    } else if (len >= 3 && f[0] == 0xFF && f[1] == 0xD8) {
+        err = "JPEG decode is not implemented (DESIGN.md row N2)";
+        return ROSY_TEX_ERR_DECODE;
+    } else if (ends_with(".rgba8")) {
+        if (len >= 8) {
+            memcpy(&w, &f[0], 4);
+            memcpy(&h, &f[4], 4);
+            if (w && h && (size_t)w * h * 4 + 8 == len) {
+                rgba.assign(f.begin() + 8, f.end());
+                rc = ROSY_TEX_OK;
+            }
+        }
+    } else if (ends_with(".tga") || name.empty()) {
+        rc = decode_tga(f, rgba, w, h);
+    }
+    if (rc != ROSY_TEX_OK) err = "unsupported or corrupt image '" + name + "'";
+    return rc;
+}
+
+int load_image(const char* path, std::vector<uint8_t>& rgba, uint32_t& w, uint32_t& h, std::string& err) {
+    std::vector<uint8_t> f;
+    if (!read_file(path, f)) {
+        err = std::string("cannot read '") + path + "'";
+        return ROSY_TEX_ERR_IO;
+    }
+    return decode_image_memory(f.data(), f.size(), path, rgba, w, h, err);
+}
+
+}  // namespace rosy_tex

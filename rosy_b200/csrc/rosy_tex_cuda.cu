@@ -1,0 +1,708 @@
+// rosy_tex_cuda.cu - C-ABI implementation (include/rosy_tex_cuda.h): device selection, buffer
+// pools, the DDS container writer, the single-texture entry points that replace the NVTT calls of
+// /root/reference/src/Packager/Packager.cpp:216-308, and the per-texture multi-GPU work queue.
+//
+// No CPU fallback exists anywhere in this file: without an sm_100 device the compute entry
+// points return ROSY_TEX_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "tex_internal.h"
+
+namespace rosy_tex {
+
+int load_image(const char* path, std::vector<uint8_t>& rgba, uint32_t& w, uint32_t& h, std::string& err);
+int mips_upload_tables();
+
+namespace {
+
+thread_local std::string t_error = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int status, const std::string& msg) {
+    t_error = msg;
+    return status;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(ROSY_TEX_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU_TRY(call)                                          \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
+    } while (0)
+
+// One in-flight texture: a stream plus grow-only device buffers.
+struct Slot {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint8_t *d_in = nullptr, *d_chain = nullptr, *d_scratch = nullptr, *d_blocks = nullptr;
+    size_t cap_in = 0, cap_chain = 0, cap_scratch = 0, cap_blocks = 0;
+    bool busy = false;
+};
+
+struct Job {
+    std::string path;  // non-empty: file job
+    std::string dds_path;
+    rosy_tex_desc desc;
+    const uint8_t* rgba = nullptr;
+    void* out = nullptr;
+    size_t cap = 0;
+    size_t* len = nullptr;
+};
+
+struct State {
+    std::mutex mu;
+    std::condition_variable cv;
+    bool inited = false;
+    rosy_tex_config cfg;
+    std::vector<int> devices;
+    std::deque<Slot> slots;  // deque: references stay valid when the queue adds its own slots
+    std::vector<int> tables_ready;  // device ordinals with constant tables uploaded
+    // work queue
+    std::deque<Job> queue;
+    std::vector<std::thread> workers;
+    int running = 0;
+    int first_error = 0;
+    std::string first_error_msg;
+    bool stop = false;
+};
+State& st() {
+    static State s;
+    return s;
+}
+
+int env_enum(const char* name, const char* const* names, int n, int dflt) {
+    const char* e = getenv(name);
+    if (!e) return dflt;
+    for (int i = 0; i < n; i++)
+        if (!strcasecmp(e, names[i])) return i;
+    return dflt;
+}
+
+int ensure_tables_locked(State& s, int device) {
+    for (int d : s.tables_ready)
+        if (d == device) return ROSY_TEX_OK;
+    if (bc7_upload_tables() != 0 || mips_upload_tables() != 0)
+        return fail(ROSY_TEX_ERR_CUDA, std::string("table upload: ") + cudaGetErrorString(cudaGetLastError()));
+    s.tables_ready.push_back(device);
+    return ROSY_TEX_OK;
+}
+
+int init_locked(State& s, const rosy_tex_config* user) {
+    if (s.inited) return ROSY_TEX_OK;
+    rosy_tex_config c;
+    memset(&c, 0, sizeof c);
+    c.quality = ROSY_TEX_QUALITY_NORMAL;
+    c.normalize = ROSY_TEX_NORMALIZE_UNPACK;
+    c.streams_per_device = 2;
+    if (user) {
+        size_t n = user->struct_size ? user->struct_size : sizeof c;
+        if (n > sizeof c) n = sizeof c;
+        rosy_tex_config u;
+        memset(&u, 0, sizeof u);
+        memcpy(&u, user, n);
+        c.num_devices = u.num_devices;
+        memcpy(c.devices, u.devices, sizeof c.devices);
+        c.quality = u.quality;
+        memcpy(c.format_for_kind, u.format_for_kind, sizeof c.format_for_kind);
+        c.normalize = u.normalize;
+        if (u.streams_per_device > 0) c.streams_per_device = u.streams_per_device;
+    }
+    static const char* const qn[] = {"fast", "normal", "high"};
+    static const char* const fn[] = {"bc7", "bc5", "bc4"};
+    static const char* const nn[] = {"off", "unpack"};
+    c.quality = env_enum("ROSY_TEX_QUALITY", qn, 3, c.quality);
+    c.format_for_kind[ROSY_TEX_KIND_COLOR] = env_enum("ROSY_TEX_FORMAT_COLOR", fn, 3, c.format_for_kind[0]);
+    c.format_for_kind[ROSY_TEX_KIND_NORMAL_MAP] = env_enum("ROSY_TEX_FORMAT_NORMAL", fn, 3, c.format_for_kind[1]);
+    c.format_for_kind[ROSY_TEX_KIND_METALLIC_ROUGHNESS] = env_enum("ROSY_TEX_FORMAT_MR", fn, 3, c.format_for_kind[2]);
+    c.format_for_kind[ROSY_TEX_KIND_MIXMAP] = env_enum("ROSY_TEX_FORMAT_MIXMAP", fn, 3, c.format_for_kind[3]);
+    c.normalize = env_enum("ROSY_TEX_NORMALIZE", nn, 2, c.normalize);
+    if (const char* e = getenv("ROSY_TEX_DEVICES")) {
+        c.num_devices = 0;
+        for (const char* p = e; *p && c.num_devices < ROSY_TEX_MAX_DEVICES;) {
+            c.devices[c.num_devices++] = atoi(p);
+            while (*p && *p != ',') p++;
+            if (*p == ',') p++;
+        }
+    }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(ROSY_TEX_ERR_NO_DEVICE, "no CUDA device is visible (there is no CPU fallback)");
+    }
+    std::vector<int> want;
+    if (c.num_devices > 0)
+        want.assign(c.devices, c.devices + c.num_devices);
+    else
+        for (int d = 0; d < count; d++) want.push_back(d);
+    s.devices.clear();
+    for (int d : want) {
+        int major = 0;
+        if (d < 0 || d >= count) continue;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major == 10)
+            s.devices.push_back(d);
+    }
+    if (s.devices.empty())
+        return fail(ROSY_TEX_ERR_NO_DEVICE, "no sm_100 (Blackwell B200) device among the visible devices (there is no CPU fallback)");
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (int d : s.devices) {
+        CU_TRY(cudaSetDevice(d));
+        int rc = ensure_tables_locked(s, d);
+        if (rc) return rc;
+        for (int k = 0; k < c.streams_per_device; k++) {
+            Slot sl;
+            sl.device = d;
+            CU_TRY(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+            s.slots.push_back(sl);
+        }
+    }
+    cudaSetDevice(prev);
+    s.cfg = c;
+    s.inited = true;
+    return ROSY_TEX_OK;
+}
+
+int ensure_init() {
+    State& s = st();
+    std::lock_guard<std::mutex> g(s.mu);
+    return init_locked(s, nullptr);
+}
+
+struct Resolved {
+    uint32_t w, h;
+    bool normal_map;
+    int format, quality, normalize;
+};
+
+int resolve(const rosy_tex_desc* d, Resolved& r) {
+    if (!d || d->width == 0 || d->height == 0) return fail(ROSY_TEX_ERR_ARG, "null descriptor or zero extent");
+    if (d->width > 32768 || d->height > 32768) return fail(ROSY_TEX_ERR_ARG, "extent above 32768");
+    if (d->kind < 0 || d->kind > 3) return fail(ROSY_TEX_ERR_ARG, "bad kind");
+    const State& s = st();
+    r.w = d->width;
+    r.h = d->height;
+    r.normal_map = d->kind == ROSY_TEX_KIND_NORMAL_MAP;
+    r.format = d->format >= 0 ? d->format : (s.inited ? s.cfg.format_for_kind[d->kind] : ROSY_TEX_FORMAT_BC7);
+    r.quality = d->quality >= 0 ? d->quality : (s.inited ? s.cfg.quality : ROSY_TEX_QUALITY_NORMAL);
+    r.normalize = d->normalize >= 0 ? d->normalize : (s.inited ? s.cfg.normalize : ROSY_TEX_NORMALIZE_UNPACK);
+    if (r.format > 2 || r.quality > 2 || r.normalize > 1) return fail(ROSY_TEX_ERR_ARG, "bad format / quality / normalize");
+    return ROSY_TEX_OK;
+}
+
+size_t block_bytes(int format) { return format == ROSY_TEX_FORMAT_BC4 ? 8 : 16; }
+
+void put32(uint8_t* p, uint32_t v) {
+    p[0] = (uint8_t)v;
+    p[1] = (uint8_t)(v >> 8);
+    p[2] = (uint8_t)(v >> 16);
+    p[3] = (uint8_t)(v >> 24);
+}
+
+// Context::outputHeader (Packager.cpp:237 / :286): 'DDS ' + DDS_HEADER + DDS_HEADER_DXT10, laid out
+// as the Engine's reader expects (src/libs/dds_formats.hpp:251-311, src/libs/dds.hpp:415-440).
+void write_dds_header(const Resolved& r, int levels, uint8_t* h) {
+    memset(h, 0, ROSY_TEX_DDS_HEADER_BYTES);
+    memcpy(h, "DDS ", 4);
+    put32(h + 4, 124);                                                // dwSize
+    put32(h + 8, 0x1 | 0x2 | 0x4 | 0x1000 | 0x20000 | 0x80000);       // CAPS|HEIGHT|WIDTH|PIXELFORMAT|MIPMAPCOUNT|LINEARSIZE
+    put32(h + 12, r.h);
+    put32(h + 16, r.w);
+    put32(h + 20, (uint32_t)(((r.w + 3) / 4) * ((r.h + 3) / 4) * block_bytes(r.format)));
+    put32(h + 28, (uint32_t)levels);
+    put32(h + 76, 32);                                                // ddspf.dwSize
+    put32(h + 80, 0x4);                                               // DDPF_FOURCC
+    memcpy(h + 84, "DX10", 4);
+    put32(h + 108, 0x1000 | 0x400000 | 0x8);                          // TEXTURE | MIPMAP | COMPLEX
+    put32(h + 128, r.format == ROSY_TEX_FORMAT_BC7 ? 98u : (r.format == ROSY_TEX_FORMAT_BC5 ? 83u : 80u));
+    put32(h + 132, 3);                                                // D3D10_RESOURCE_DIMENSION_TEXTURE2D
+    put32(h + 140, 1);                                                // arraySize
+}
+
+int grow(uint8_t*& p, size_t& cap, size_t need) {
+    if (need <= cap) return ROSY_TEX_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ROSY_TEX_ERR_NOMEM, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cap = need;
+    return ROSY_TEX_OK;
+}
+
+int encode_on_stream(const Chain& c, const Resolved& r, const uint8_t* d_rgba, uint8_t* d_chain, void* d_scratch,
+                     uint8_t* d_blocks, cudaStream_t stream, bool do_mips, bool do_blocks) {
+    if (do_mips && c.levels > 1 || (do_mips && r.normal_map)) {
+        int n = launch_mips(c, r.normal_map, r.normalize, d_rgba, d_chain, d_scratch, stream);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "mip kernels");
+        g_launches += (uint64_t)n;
+    }
+    if (do_blocks) {
+        const uint8_t* level0 = r.normal_map ? nullptr : d_rgba;
+        int n;
+        if (r.format == ROSY_TEX_FORMAT_BC7)
+            n = launch_bc7(c, 0, c.levels, bc7_tier(r.quality), level0, d_chain, d_blocks, stream);
+        else
+            n = launch_bc45(c, 0, c.levels, r.format == ROSY_TEX_FORMAT_BC5, level0, d_chain, d_blocks, stream);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "encoder kernel");
+        g_launches += (uint64_t)n;
+    }
+    return ROSY_TEX_OK;
+}
+
+Slot* acquire_slot() {
+    State& s = st();
+    std::unique_lock<std::mutex> g(s.mu);
+    for (;;) {
+        for (Slot& sl : s.slots)
+            if (!sl.busy) {
+                sl.busy = true;
+                return &sl;
+            }
+        s.cv.wait(g);
+    }
+}
+void release_slot(Slot* sl) {
+    State& s = st();
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        sl->busy = false;
+    }
+    s.cv.notify_all();
+}
+
+enum What { WHAT_DDS, WHAT_MIPS, WHAT_LEVEL };
+
+// host buffers in, host buffers out, on one slot
+int run_host(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len) {
+    Chain c = make_chain(r.w, r.h);
+    if (what == WHAT_LEVEL) {  // a single level, no mip chain
+        c.levels = 1;
+        c.total_px = (uint64_t)r.w * r.h;
+        c.total_blocks = (uint64_t)c.lv[0].bw * c.lv[0].bh;
+    }
+    const size_t in_bytes = (size_t)r.w * r.h * 4, chain_bytes = (size_t)c.total_px * 4;
+    const size_t blk_bytes = (size_t)c.total_blocks * block_bytes(r.format);
+    const size_t need = what == WHAT_DDS ? ROSY_TEX_DDS_HEADER_BYTES + blk_bytes : (what == WHAT_MIPS ? chain_bytes : blk_bytes);
+    if (len) *len = need;
+    if (!rgba || !out || cap < need) return fail(ROSY_TEX_ERR_ARG, "null buffer or output capacity too small");
+    CU_TRY(cudaSetDevice(sl->device));
+    int rc;
+    if ((rc = grow(sl->d_in, sl->cap_in, in_bytes))) return rc;
+    if ((rc = grow(sl->d_chain, sl->cap_chain, chain_bytes))) return rc;
+    if ((rc = grow(sl->d_blocks, sl->cap_blocks, blk_bytes))) return rc;
+    const size_t sc = mips_scratch_bytes(c);
+    if (sc > sl->cap_scratch) {
+        if ((rc = grow(sl->d_scratch, sl->cap_scratch, sc))) return rc;
+        CU_TRY(cudaMemsetAsync(sl->d_scratch, 0, 256, sl->stream));  // the fused kernel's ticket
+    }
+    CU_TRY(cudaMemcpyAsync(sl->d_in, rgba, in_bytes, cudaMemcpyHostToDevice, sl->stream));
+    if (what == WHAT_LEVEL) {
+        Resolved rl = r;
+        rl.normal_map = false;  // the level is taken as is
+        if ((rc = encode_on_stream(c, rl, sl->d_in, sl->d_chain, sl->d_scratch, sl->d_blocks, sl->stream, false, true)))
+            return rc;
+        CU_TRY(cudaMemcpyAsync(out, sl->d_blocks, blk_bytes, cudaMemcpyDeviceToHost, sl->stream));
+    } else if (what == WHAT_MIPS) {
+        if ((rc = encode_on_stream(c, r, sl->d_in, sl->d_chain, sl->d_scratch, sl->d_blocks, sl->stream, true, false)))
+            return rc;
+        if (r.normal_map) {
+            CU_TRY(cudaMemcpyAsync(out, sl->d_chain, chain_bytes, cudaMemcpyDeviceToHost, sl->stream));
+        } else {  // colour level 0 is the input itself (Packager.cpp:245 at mip 0)
+            memcpy(out, rgba, in_bytes);
+            if (chain_bytes > in_bytes)
+                CU_TRY(cudaMemcpyAsync(out + in_bytes, sl->d_chain + in_bytes, chain_bytes - in_bytes,
+                                       cudaMemcpyDeviceToHost, sl->stream));
+        }
+    } else {
+        if ((rc = encode_on_stream(c, r, sl->d_in, sl->d_chain, sl->d_scratch, sl->d_blocks, sl->stream, true, true)))
+            return rc;
+        write_dds_header(r, c.levels, out);
+        CU_TRY(cudaMemcpyAsync(out + ROSY_TEX_DDS_HEADER_BYTES, sl->d_blocks, blk_bytes, cudaMemcpyDeviceToHost, sl->stream));
+    }
+    CU_TRY(cudaStreamSynchronize(sl->stream));
+    return ROSY_TEX_OK;
+}
+
+int run_host_any(const rosy_tex_desc* desc, What what, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
+    int rc = ensure_init();
+    if (rc) return rc;
+    Resolved r;
+    if ((rc = resolve(desc, r))) return rc;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    Slot* sl = acquire_slot();
+    rc = run_host(sl, r, what, rgba, static_cast<uint8_t*>(out), cap, len);
+    release_slot(sl);
+    cudaSetDevice(prev);
+    return rc;
+}
+
+std::string replace_extension(const std::string& path, const char* ext) {
+    const size_t slash = path.find_last_of("/\\");
+    const size_t dot = path.find_last_of('.');
+    if (dot == std::string::npos || (slash != std::string::npos && dot < slash)) return path + ext;
+    return path.substr(0, dot) + ext;
+}
+
+// the whole of generate_srgb_texture / generate_normal_map_texture for one file, on one slot
+int run_file(Slot* sl, const std::string& path, int kind, const std::string& dds_path_in) {
+    std::vector<uint8_t> rgba;
+    uint32_t w = 0, h = 0;
+    std::string err;
+    int rc = load_image(path.c_str(), rgba, w, h, err);  // nvtt::Surface::load, Packager.cpp:222
+    if (rc) return fail(rc, err);
+    rosy_tex_desc d = {w, h, kind, -1, -1, -1};
+    Resolved r;
+    if ((rc = resolve(&d, r))) return rc;
+    std::vector<uint8_t> dds(ROSY_TEX_DDS_HEADER_BYTES + (size_t)make_chain(w, h).total_blocks * block_bytes(r.format));
+    size_t len = 0;
+    if ((rc = run_host(sl, r, WHAT_DDS, rgba.data(), dds.data(), dds.size(), &len))) return rc;
+    const std::string dds_path = dds_path_in.empty() ? replace_extension(path, ".dds") : dds_path_in;  // :231
+    const std::string tmp = dds_path + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return fail(ROSY_TEX_ERR_IO, "cannot create '" + tmp + "'");
+    const bool ok = fwrite(dds.data(), 1, len, f) == len;
+    if (fclose(f) != 0 || !ok || rename(tmp.c_str(), dds_path.c_str()) != 0) {
+        remove(tmp.c_str());
+        return fail(ROSY_TEX_ERR_IO, "cannot write '" + dds_path + "'");
+    }
+    return ROSY_TEX_OK;
+}
+
+void worker_main(Slot* sl) {
+    State& s = st();
+    for (;;) {
+        Job job;
+        {
+            std::unique_lock<std::mutex> g(s.mu);
+            s.cv.wait(g, [&] { return s.stop || !s.queue.empty(); });
+            if (s.stop && s.queue.empty()) return;
+            job = std::move(s.queue.front());
+            s.queue.pop_front();
+            s.running++;
+        }
+        int rc;
+        if (!job.path.empty()) {
+            rc = run_file(sl, job.path, job.desc.kind, job.dds_path);
+        } else {
+            Resolved r;
+            rc = resolve(&job.desc, r);
+            if (!rc) rc = run_host(sl, r, WHAT_DDS, job.rgba, static_cast<uint8_t*>(job.out), job.cap, job.len);
+        }
+        {
+            std::lock_guard<std::mutex> g(s.mu);
+            if (rc && !s.first_error) {
+                s.first_error = rc;
+                s.first_error_msg = t_error;
+            }
+            s.running--;
+        }
+        s.cv.notify_all();
+    }
+}
+
+int enqueue(Job&& job) {
+    int rc = ensure_init();
+    if (rc) return rc;
+    State& s = st();
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        if (s.workers.empty()) {
+            // one worker thread per slot; the queue's slots are separate from the synchronous ones
+            const size_t n = s.slots.size();
+            for (size_t i = 0; i < n; i++) {
+                Slot sl;
+                sl.device = s.slots[i].device;
+                sl.busy = true;  // owned by its worker
+                cudaSetDevice(sl.device);
+                cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking);
+                s.slots.push_back(sl);
+            }
+            for (size_t i = 0; i < n; i++) s.workers.emplace_back(worker_main, &s.slots[n + i]);
+        }
+        s.queue.push_back(std::move(job));
+    }
+    s.cv.notify_all();
+    return ROSY_TEX_OK;
+}
+
+}  // namespace
+
+Chain make_chain(uint32_t w, uint32_t h) {
+    Chain c;
+    memset(&c, 0, sizeof c);
+    uint64_t px = 0, blk = 0;
+    int l = 0;
+    for (;; l++) {
+        Level& L = c.lv[l];
+        L.w = w;
+        L.h = h;
+        L.bw = (w + 3) / 4;
+        L.bh = (h + 3) / 4;
+        L.px_offset = px;
+        L.blk_offset = blk;
+        px += (uint64_t)w * h;
+        blk += (uint64_t)L.bw * L.bh;
+        if (w == 1 && h == 1) break;
+        w = w / 2 > 1 ? w / 2 : 1;  // nvtt::Surface::countMipmaps / buildNextMipmap extents
+        h = h / 2 > 1 ? h / 2 : 1;
+    }
+    c.levels = l + 1;
+    c.total_px = px;
+    c.total_blocks = blk;
+    return c;
+}
+
+}  // namespace rosy_tex
+
+using namespace rosy_tex;
+
+extern "C" {
+
+int rosy_tex_init(const rosy_tex_config* config) {
+    State& s = st();
+    std::lock_guard<std::mutex> g(s.mu);
+    return init_locked(s, config);
+}
+
+void rosy_tex_shutdown(void) {
+    State& s = st();
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        s.stop = true;
+    }
+    s.cv.notify_all();
+    for (std::thread& t : s.workers) t.join();
+    std::lock_guard<std::mutex> g(s.mu);
+    s.workers.clear();
+    for (Slot& sl : s.slots) {
+        cudaSetDevice(sl.device);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
+        cudaFree(sl.d_in);
+        cudaFree(sl.d_chain);
+        cudaFree(sl.d_scratch);
+        cudaFree(sl.d_blocks);
+    }
+    s.slots.clear();
+    s.devices.clear();
+    s.queue.clear();
+    s.stop = false;
+    s.inited = false;
+    s.first_error = 0;
+}
+
+int rosy_tex_device_count(void) {
+    if (ensure_init()) return 0;
+    return (int)st().devices.size();
+}
+
+const char* rosy_tex_last_error(void) { return t_error.c_str(); }
+
+const char* rosy_tex_status_string(int status) {
+    switch (status) {
+        case ROSY_TEX_OK: return "ok";
+        case ROSY_TEX_ERR_IO: return "io error";
+        case ROSY_TEX_ERR_DECODE: return "image decode error";
+        case ROSY_TEX_ERR_ARG: return "invalid argument";
+        case ROSY_TEX_ERR_CUDA: return "cuda error";
+        case ROSY_TEX_ERR_NO_DEVICE: return "no sm_100 device (no CPU fallback)";
+        case ROSY_TEX_ERR_NOMEM: return "out of device memory";
+        default: return "unknown status";
+    }
+}
+
+int rosy_tex_generate_texture_file(const char* image_path, int kind, const char* dds_path) {
+    if (!image_path) return fail(ROSY_TEX_ERR_ARG, "null path");
+    if (kind < 0 || kind > 3) return fail(ROSY_TEX_ERR_ARG, "bad kind");
+    int rc = ensure_init();
+    if (rc) return rc;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    Slot* sl = acquire_slot();
+    rc = run_file(sl, image_path, kind, dds_path ? dds_path : "");
+    release_slot(sl);
+    cudaSetDevice(prev);
+    return rc;
+}
+
+int rosy_tex_generate_srgb_texture(const char* image_path) {
+    return rosy_tex_generate_texture_file(image_path, ROSY_TEX_KIND_COLOR, nullptr);
+}
+
+int rosy_tex_generate_normal_map_texture(const char* image_path) {
+    return rosy_tex_generate_texture_file(image_path, ROSY_TEX_KIND_NORMAL_MAP, nullptr);
+}
+
+int rosy_tex_load_image(const char* image_path, uint8_t** rgba, uint32_t* width, uint32_t* height) {
+    if (!image_path || !rgba || !width || !height) return fail(ROSY_TEX_ERR_ARG, "null argument");
+    std::vector<uint8_t> px;
+    std::string err;
+    int rc = load_image(image_path, px, *width, *height, err);
+    if (rc) return fail(rc, err);
+    *rgba = static_cast<uint8_t*>(malloc(px.size()));
+    if (!*rgba) return fail(ROSY_TEX_ERR_NOMEM, "malloc");
+    memcpy(*rgba, px.data(), px.size());
+    return ROSY_TEX_OK;
+}
+
+void rosy_tex_free_image(uint8_t* rgba) { free(rgba); }
+
+int rosy_tex_count_mipmaps(uint32_t width, uint32_t height) {
+    if (!width || !height) return 0;
+    return make_chain(width, height).levels;
+}
+
+void rosy_tex_level_extent(uint32_t width, uint32_t height, int level, uint32_t* w, uint32_t* h) {
+    for (int i = 0; i < level; i++) {
+        width = width / 2 > 1 ? width / 2 : 1;
+        height = height / 2 > 1 ? height / 2 : 1;
+    }
+    if (w) *w = width;
+    if (h) *h = height;
+}
+
+size_t rosy_tex_dds_size(const rosy_tex_desc* desc) {
+    Resolved r;
+    if (resolve(desc, r)) return 0;
+    return ROSY_TEX_DDS_HEADER_BYTES + (size_t)make_chain(r.w, r.h).total_blocks * block_bytes(r.format);
+}
+
+size_t rosy_tex_chain_size(uint32_t width, uint32_t height) {
+    if (!width || !height) return 0;
+    return (size_t)make_chain(width, height).total_px * 4;
+}
+
+int rosy_tex_dds_header(const rosy_tex_desc* desc, uint8_t* out148) {
+    Resolved r;
+    int rc = resolve(desc, r);
+    if (rc) return rc;
+    if (!out148) return fail(ROSY_TEX_ERR_ARG, "null buffer");
+    write_dds_header(r, make_chain(r.w, r.h).levels, out148);
+    return ROSY_TEX_OK;
+}
+
+int rosy_tex_encode_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
+    return run_host_any(desc, WHAT_DDS, rgba, out, cap, len);
+}
+
+int rosy_tex_mips_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len) {
+    return run_host_any(desc, WHAT_MIPS, rgba, out, cap, len);
+}
+
+int rosy_tex_compress_level_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
+    return run_host_any(desc, WHAT_LEVEL, rgba, out, cap, len);
+}
+
+int rosy_tex_submit(const char* image_path, int kind) {
+    if (!image_path) return fail(ROSY_TEX_ERR_ARG, "null path");
+    if (kind < 0 || kind > 3) return fail(ROSY_TEX_ERR_ARG, "bad kind");
+    Job j;
+    j.path = image_path;
+    memset(&j.desc, 0, sizeof j.desc);
+    j.desc.kind = kind;
+    return enqueue(std::move(j));
+}
+
+int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
+    Resolved r;
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((rc = resolve(desc, r))) return rc;
+    if (!rgba || !out) return fail(ROSY_TEX_ERR_ARG, "null buffer");
+    Job j;
+    j.desc = *desc;
+    j.rgba = rgba;
+    j.out = out;
+    j.cap = cap;
+    j.len = len;
+    return enqueue(std::move(j));
+}
+
+int rosy_tex_wait_all(void) {
+    State& s = st();
+    std::unique_lock<std::mutex> g(s.mu);
+    s.cv.wait(g, [&] { return s.queue.empty() && s.running == 0; });
+    const int rc = s.first_error;
+    if (rc) t_error = s.first_error_msg;
+    s.first_error = 0;
+    return rc;
+}
+
+void* rosy_tex_alloc_host(size_t bytes) {
+    if (ensure_init()) return nullptr;
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void rosy_tex_free_host(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+size_t rosy_tex_device_scratch_size(const rosy_tex_desc* desc) {
+    Resolved r;
+    if (resolve(desc, r)) return 0;
+    return mips_scratch_bytes(make_chain(r.w, r.h));
+}
+
+static int device_common(const rosy_tex_desc* desc, Resolved& r) {
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((rc = resolve(desc, r))) return rc;
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    State& s = st();
+    std::lock_guard<std::mutex> g(s.mu);
+    return ensure_tables_locked(s, dev);
+}
+
+int rosy_tex_mips_device(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain, void* d_scratch, void* stream) {
+    Resolved r;
+    int rc = device_common(desc, r);
+    if (rc) return rc;
+    if (!d_rgba || !d_chain || !d_scratch) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba), static_cast<uint8_t*>(d_chain),
+                            d_scratch, nullptr, static_cast<cudaStream_t>(stream), true, false);
+}
+
+int rosy_tex_blocks_device(const rosy_tex_desc* desc, const void* d_rgba, const void* d_chain, void* d_blocks, void* stream) {
+    Resolved r;
+    int rc = device_common(desc, r);
+    if (rc) return rc;
+    if (!d_rgba || !d_chain || !d_blocks) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba),
+                            const_cast<uint8_t*>(static_cast<const uint8_t*>(d_chain)), nullptr,
+                            static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), false, true);
+}
+
+int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain, void* d_scratch, void* d_blocks,
+                           void* stream) {
+    Resolved r;
+    int rc = device_common(desc, r);
+    if (rc) return rc;
+    if (!d_rgba || !d_chain || !d_scratch || !d_blocks) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba), static_cast<uint8_t*>(d_chain),
+                            d_scratch, static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), true, true);
+}
+
+uint64_t rosy_tex_kernel_launches(void) { return g_launches.load(); }
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+// tex_internal.h - shared between the kernels and the C-ABI host code of librosy_tex_cuda.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rosy_tex_cuda.h"
+
+namespace rosy_tex {
+
+// One mip level as the kernels see it.  The chain buffer holds RGBA8 levels back to back,
+// level 0 first (offsets in pixels); blocks of all levels are emitted back to back, largest
+// level first (dds.hpp:551-565 consumer contract).
+struct Level {
+    uint32_t w, h;        // extent in pixels
+    uint32_t bw, bh;      // extent in 4x4 blocks
+    uint64_t px_offset;   // first pixel of this level in the chain buffer
+    uint64_t blk_offset;  // first block of this level in the block stream
+};
+
+struct Chain {
+    int levels;
+    uint32_t pad;
+    uint64_t total_px;
+    uint64_t total_blocks;
+    Level lv[ROSY_TEX_MAX_LEVELS];
+};
+
+Chain make_chain(uint32_t w, uint32_t h);
+
+// Search effort of the BC7 encoder ("spec v1").  Mirrors nvtt::Quality_*.
+struct Bc7Tier {
+    int n1, n3, n0, n2, n7;  // partitions refined in modes 1,3,0,2,7 (0 = mode off)
+    int rot5;                // rotations tried in mode 5 (1 or 4)
+    int rot4;                // rotations tried in mode 4 (0 = off), both index selectors
+    int ls_rounds;           // least-squares refinement rounds per fit
+    int pb_search;           // 1: evaluate every p-bit combination
+};
+Bc7Tier bc7_tier(int quality);
+
+// ---- kernel launchers (each returns the number of kernels it launched, or -1 on error) ----
+// mip_kernels.cu
+int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
+                uint8_t* d_chain, void* d_scratch, cudaStream_t s);
+size_t mips_scratch_bytes(const Chain& c);
+// bc45_encode.cu
+int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
+                const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
+// bc7_encode.cu
+int launch_bc7(const Chain& c, int first_level, int num_levels, const Bc7Tier& t,
+               const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
+int bc7_upload_tables();   // per device, once
+int mips_upload_tables();  // per device, once
+
+}  // namespace rosy_tex

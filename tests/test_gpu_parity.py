@@ -1,0 +1,229 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle.
+
+Bars (north_star / SURVEY.md 8c):
+  * mip levels: identical extents and count, <= 1 LSB per 8-bit channel
+  * BC4 / BC5: bit exact (integer algorithm of stb_dxt.h)
+  * BC7: every block valid and decodable; PSNR >= oracle - 0.1 dB at the matched tier.  The
+    kernel implements the same search specification as the oracle, so we additionally require
+    bit-exact blocks and report it separately from the PSNR gate.
+"""
+import numpy as np
+import pytest
+
+from conftest import max_abs_diff
+
+pytestmark = pytest.mark.gpu
+
+KINDS = [("albedo", 0), ("albedo", 7), ("normal", 1), ("metal_rough", 2), ("random", 3)]
+
+
+def _chain_check(tex, oracle, img, kind, normalize=-1):
+    got = tex.mips_rgba8(img, kind, normalize)
+    want = oracle.mip_chain(img, oracle.KIND_NORMAL if kind == tex.KIND_NORMAL_MAP else oracle.KIND_SRGB,
+                            oracle.NORMALIZE_UNPACK if normalize != 0 else oracle.NORMALIZE_OFF)
+    assert len(got) == len(want) == oracle.count_mipmaps(img.shape[1], img.shape[0])
+    worst = 0
+    for l, (g, w) in enumerate(zip(got, want)):
+        assert g.shape == w.shape, f"level {l} extent {g.shape} != {w.shape}"
+        d = max_abs_diff(g, w)
+        assert d <= 1, f"level {l}: max abs diff {d} LSB"
+        worst = max(worst, d)
+    return worst
+
+
+@pytest.mark.parametrize("size", [(256, 256), (1024, 1024), (512, 128), (64, 64)])
+@pytest.mark.parametrize("name,index", [("albedo", 0), ("albedo", 7), ("metal_rough", 2), ("random", 3)])
+def test_colour_mip_chain_within_1lsb(tex, oracle, synth, size, name, index):
+    img = synth.make(name, size[0], size[1], index)
+    _chain_check(tex, oracle, img, tex.KIND_COLOR)
+
+
+@pytest.mark.parametrize("size", [(256, 256), (1024, 1024), (128, 512)])
+@pytest.mark.parametrize("normalize", [1, 0])
+def test_normal_mip_chain_within_1lsb(tex, oracle, synth, size, normalize):
+    img = synth.normal(size[0], size[1], 1)
+    _chain_check(tex, oracle, img, tex.KIND_NORMAL_MAP, normalize)
+
+
+@pytest.mark.parametrize("size", [(1, 1), (2, 2), (3, 5), (17, 9), (100, 60), (255, 257), (640, 360), (1, 64), (64, 1)])
+def test_mip_chain_ragged_extents(tex, oracle, synth, size):
+    """odd / non-square / non-power-of-two: generic path, polyphase box (H7)"""
+    w, h = size
+    _chain_check(tex, oracle, synth.albedo(w, h, 7 if w > 8 else 0), tex.KIND_COLOR)
+    _chain_check(tex, oracle, synth.normal(w, h, 1), tex.KIND_NORMAL_MAP)
+
+
+def test_fused_and_generic_mip_paths_agree(tex, oracle, synth, monkeypatch):
+    """the TMA-fused single-launch kernel and the per-level kernels are both within 1 LSB"""
+    import subprocess, sys, os, textwrap
+
+    code = textwrap.dedent(
+        """
+        import numpy as np, sys
+        sys.path.insert(0, %r)
+        from rosy_b200 import texture as T, synth as S
+        import oracle as O
+        img = S.albedo(512, 512, 7)
+        got = T.mips_rgba8(img, T.KIND_COLOR)
+        want = O.mip_chain(img, O.KIND_SRGB)
+        print(max(int(np.abs(g.astype(int) - w.astype(int)).max()) for g, w in zip(got, want)))
+        """
+        % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    )
+    for mode in ("generic", "fused"):
+        env = dict(os.environ, ROSY_TEX_MIPS=mode)
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr[-2000:]
+        assert int(out.stdout.strip().splitlines()[-1]) <= 1, (mode, out.stdout)
+
+
+def test_known_answers(tex, synth):
+    """C6: constants survive every level; flat normal stays (128,128,255)"""
+    levels = tex.mips_rgba8(synth.constant(256, 256, (187, 187, 187, 255)), tex.KIND_COLOR)
+    for l in levels:
+        assert (l == np.array([187, 187, 187, 255], dtype=np.uint8)).all()
+    levels = tex.mips_rgba8(synth.constant(128, 128, (128, 128, 255, 255)), tex.KIND_NORMAL_MAP)
+    for l in levels:
+        assert (l == np.array([128, 128, 255, 255], dtype=np.uint8)).all()
+    # fully transparent texels carry no colour into the mips; an all-transparent image gives rgb = 0
+    img = synth.constant(64, 64, (200, 10, 10, 0))
+    levels = tex.mips_rgba8(img, tex.KIND_COLOR)
+    assert (levels[1] == 0).all()
+
+
+@pytest.mark.parametrize("fmt_name", ["bc5", "bc4"])
+@pytest.mark.parametrize("name,index,size", [("normal", 1, (256, 256)), ("random", 3, (128, 64)), ("albedo", 0, (30, 18))])
+def test_bc45_bit_exact(tex, oracle, synth, fmt_name, name, index, size):
+    fmt_t = tex.FORMAT_BC5 if fmt_name == "bc5" else tex.FORMAT_BC4
+    fmt_o = oracle.FMT_BC5 if fmt_name == "bc5" else oracle.FMT_BC4
+    img = synth.make(name, size[0], size[1], index)
+    got = tex.compress_level(img, fmt_t)
+    want = oracle.encode_image(img, fmt_o)
+    assert got.shape == want.shape
+    assert (got == want).all()
+
+
+@pytest.mark.parametrize("quality", [0, 1, 2])
+@pytest.mark.parametrize("name,index", KINDS)
+def test_bc7_level_parity(tex, oracle, synth, quality, name, index):
+    w, h = (128, 128) if quality == 2 else (256, 256)
+    img = synth.make(name, w, h, index)
+    got = tex.compress_level(img, tex.FORMAT_BC7, quality)
+    want = oracle.encode_image(img, oracle.FMT_BC7, quality)
+    modes = oracle.bc7_block_modes(got)
+    assert (modes >= 0).all(), "reserved BC7 mode emitted"
+    dec_g = oracle.decode_image(got, w, h)
+    dec_o = oracle.decode_image(want, w, h)
+    p_g, p_o = oracle.psnr(img, dec_g), oracle.psnr(img, dec_o)
+    assert p_g >= p_o - 0.1, f"PSNR {p_g:.3f} dB < oracle {p_o:.3f} dB - 0.1"
+    same = (got.reshape(-1, 16) == want.reshape(-1, 16)).all(axis=1)
+    assert same.all(), f"{(~same).sum()} of {same.size} blocks differ from the oracle (PSNR {p_g:.3f} vs {p_o:.3f})"
+
+
+def test_bc7_partial_blocks_and_tiny_levels(tex, oracle, synth):
+    for (w, h) in [(1, 1), (2, 2), (3, 7), (10, 6), (33, 31)]:
+        img = synth.albedo(w, h, 7 if w > 4 else 0)
+        got = tex.compress_level(img, tex.FORMAT_BC7, 1)
+        want = oracle.encode_image(img, oracle.FMT_BC7, 1)
+        assert (got == want).all(), (w, h)
+
+
+def test_bc7_solid_and_two_colour_blocks_exact(tex, oracle):
+    rng = np.random.default_rng(5)
+    img = np.zeros((64, 64, 4), dtype=np.uint8)
+    for by in range(16):
+        for bx in range(16):
+            img[4 * by : 4 * by + 4, 4 * bx : 4 * bx + 4] = rng.integers(0, 256, 4)
+    got = tex.compress_level(img, tex.FORMAT_BC7, 1)
+    dec = oracle.decode_image(got, 64, 64)
+    assert (dec == img).all(), "solid blocks must decode exactly"
+    # opaque two-colour blocks: both colours are end points of some mode -> exact
+    img2 = np.zeros((4, 64, 4), dtype=np.uint8)
+    for bx in range(16):
+        a = np.append(rng.integers(0, 128, 3) * 2 + 1, 255)  # odd values: 7-bit + p-bit 1 exact
+        b = np.append(rng.integers(0, 128, 3) * 2 + 1, 255)
+        blk = np.where(rng.integers(0, 2, (4, 4, 1)) == 1, a, b)
+        img2[:, 4 * bx : 4 * bx + 4] = blk
+    dec2 = oracle.decode_image(tex.compress_level(img2, tex.FORMAT_BC7, 1), 64, 4)
+    assert (dec2 == img2).all()
+
+
+@pytest.mark.parametrize("kind_name,index,kind,fmt", [("albedo", 0, 0, 0), ("albedo", 7, 0, 0), ("normal", 1, 1, 0),
+                                                       ("normal", 1, 1, 1), ("metal_rough", 2, 2, 0), ("metal_rough", 2, 2, 2)])
+def test_whole_stage_dds(tex, oracle, synth, kind_name, index, kind, fmt):
+    """generate_*_texture memory to memory: container, level sizes, validity, PSNR vs the oracle"""
+    w = h = 256
+    img = synth.make(kind_name, w, h, index)
+    got = tex.encode_rgba8(img, kind, fmt, 1)
+    okind = oracle.KIND_NORMAL if kind == 1 else oracle.KIND_SRGB
+    want = oracle.generate_texture(img, okind, fmt, 1)
+    assert got.size == want.size == oracle.dds_size(w, h, fmt)
+    assert (got[:148] == want[:148]).all(), "DDS header differs from the oracle's"
+    chain = oracle.mip_chain(img, okind)
+    off = 148
+    bb = 8 if fmt == 2 else 16
+    for l, ref in enumerate(chain):
+        lh, lw = ref.shape[:2]
+        n = ((lw + 3) // 4) * ((lh + 3) // 4) * bb
+        g = got[off : off + n]
+        o = want[off : off + n]
+        if fmt == 0:
+            assert (oracle.bc7_block_modes(g) >= 0).all()
+        dg = oracle.decode_image(g, lw, lh, fmt)
+        do = oracle.decode_image(o, lw, lh, fmt)
+        ch = 4 if fmt == 0 else (2 if fmt == 1 else 1)
+        assert oracle.psnr(ref, dg, ch) >= oracle.psnr(ref, do, ch) - 0.1, f"level {l}"
+        off += n
+    assert off == got.size
+    if oracle.have_ref_dds():
+        info = oracle.ref_dds_read(got.tobytes())
+        assert info["numMips"] == len(chain) and info["width"] == w and info["height"] == h
+        assert info["format"] == {0: 98, 1: 83, 2: 80}[fmt]
+
+
+def test_file_entry_points(tex, oracle, synth, tmp_path):
+    """Packager.h:8-9 semantics: <image>.dds appears next to the image; failures raise"""
+    from PIL import Image
+
+    img = synth.albedo(128, 64, 7)
+    p = tmp_path / "albedo.png"
+    Image.fromarray(img).save(p)
+    tex.generate_srgb_texture(str(p))
+    dds = np.fromfile(tmp_path / "albedo.dds", dtype=np.uint8)
+    assert (dds == tex.encode_rgba8(img, tex.KIND_COLOR)).all()
+    nrm = synth.normal(64, 64, 1)
+    p2 = tmp_path / "n.tga"
+    hdr = bytes([0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, 64, 0, 64, 0, 32, 0x28])
+    p2.write_bytes(hdr + nrm[..., [2, 1, 0, 3]].tobytes())
+    tex.generate_normal_map_texture(str(p2))
+    dds2 = np.fromfile(tmp_path / "n.dds", dtype=np.uint8)
+    assert (dds2 == tex.encode_rgba8(nrm, tex.KIND_NORMAL_MAP)).all()
+    from rosy_b200 import RosyTexError
+
+    with pytest.raises(RosyTexError):
+        tex.generate_srgb_texture(str(tmp_path / "missing.png"))
+    assert not (tmp_path / "missing.dds").exists()
+
+
+def test_work_queue_matches_sync_and_is_deterministic(tex, synth):
+    imgs = [(synth.albedo(256, 256, i), tex.KIND_COLOR) for i in range(6)] + [(synth.normal(128, 128, 9), tex.KIND_NORMAL_MAP)]
+    q = tex.Pending()
+    for img, kind in imgs:
+        q.submit(img, kind)
+    outs = q.wait_all()
+    for (img, kind), out in zip(imgs, outs):
+        assert (out == tex.encode_rgba8(img, kind)).all()
+
+
+def test_size_independent_properties_at_full_size(tex, oracle, synth):
+    """config sizes the oracle is too slow for: structure + decodability + PSNR floor + idempotent"""
+    img = synth.normal(2048, 2048, 1)
+    a = tex.encode_rgba8(img, tex.KIND_NORMAL_MAP)
+    b = tex.encode_rgba8(img, tex.KIND_NORMAL_MAP)
+    assert (a == b).all(), "not deterministic"
+    assert a.size == 148 + 16 * oracle.chain_blocks(2048, 2048)
+    lvl0 = a[148 : 148 + 16 * 512 * 512]
+    assert (oracle.bc7_block_modes(lvl0) >= 0).all()
+    dec = oracle.decode_image(lvl0, 2048, 2048)
+    want0 = tex.mips_rgba8(img, tex.KIND_NORMAL_MAP)[0]
+    assert oracle.psnr(want0, dec) > 38.0

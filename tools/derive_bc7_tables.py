@@ -183,24 +183,28 @@ static const uint8_t BC7_ANCHOR3B[64] = {{
 }};
 #endif
 """
-    cu_hdr = body.replace("{P}", "c_") + f"""\
+    cu_hdr = body.replace("{P}", "c_ / h_") + f"""\
+// h_* are host copies (used to derive the byte-mask tables uploaded at init), c_* live in
+// constant memory.
 #pragma once
 #include <stdint.h>
-__constant__ uint16_t c_PART2_MASK[64] = {{
-{fmt([f'0x{m:04X}' for m in mask2], 8, 6)}
-}};
-__constant__ uint32_t c_PART3_MASK[64] = {{
-{fmt([f'0x{m:08X}u' for m in mask3], 4, 11)}
-}};
-__constant__ uint8_t c_ANCHOR2[64] = {{
-{fmt(anchor2)}
-}};
-__constant__ uint8_t c_ANCHOR3A[64] = {{
-{fmt(anchor3a)}
-}};
-__constant__ uint8_t c_ANCHOR3B[64] = {{
-{fmt(anchor3b)}
-}};
+#define ROSY_BC7_PART2_MASK_INIT {{ \\
+{fmt([f'0x{m:04X}' for m in mask2], 8, 6).replace(chr(10), ' ' + chr(92) + chr(10))} }}
+#define ROSY_BC7_PART3_MASK_INIT {{ \\
+{fmt([f'0x{m:08X}u' for m in mask3], 4, 11).replace(chr(10), ' ' + chr(92) + chr(10))} }}
+#define ROSY_BC7_ANCHOR2_INIT {{ \\
+{fmt(anchor2).replace(chr(10), ' ' + chr(92) + chr(10))} }}
+#define ROSY_BC7_ANCHOR3A_INIT {{ \\
+{fmt(anchor3a).replace(chr(10), ' ' + chr(92) + chr(10))} }}
+#define ROSY_BC7_ANCHOR3B_INIT {{ \\
+{fmt(anchor3b).replace(chr(10), ' ' + chr(92) + chr(10))} }}
+static const uint16_t h_PART2_MASK[64] = ROSY_BC7_PART2_MASK_INIT;
+static const uint32_t h_PART3_MASK[64] = ROSY_BC7_PART3_MASK_INIT;
+static const uint8_t h_ANCHOR2[64] = ROSY_BC7_ANCHOR2_INIT;
+static const uint8_t h_ANCHOR3A[64] = ROSY_BC7_ANCHOR3A_INIT;
+static const uint8_t h_ANCHOR3B[64] = ROSY_BC7_ANCHOR3B_INIT;
+__constant__ uint16_t c_PART2_MASK[64] = ROSY_BC7_PART2_MASK_INIT;
+__constant__ uint32_t c_PART3_MASK[64] = ROSY_BC7_PART3_MASK_INIT;
 """
     with open(os.path.join(ROOT, "oracle", "bc7_tables.h"), "w") as f:
         f.write(c_hdr)
