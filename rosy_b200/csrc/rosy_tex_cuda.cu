@@ -78,8 +78,10 @@ struct State {
     bool stop = false;
 };
 State& st() {
-    static State s;
-    return s;
+    // Leaked on purpose: worker threads may still be parked on the condition variable when the
+    // process exits without rosy_tex_shutdown(); destroying joinable std::threads would terminate().
+    static State* s = new State;
+    return *s;
 }
 
 int env_enum(const char* name, const char* const* names, int n, int dflt) {
