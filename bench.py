@@ -1,0 +1,509 @@
+#!/usr/bin/env python
+"""bench.py - headline measurement of the Packager texture stage on B200 (driver contract).
+
+Metric (BASELINE.json): BC7+mips Mpix/s.  Workload = BASELINE.json configs[4] (the throughput
+sweep: 512 synthetic 2048x2048 albedo textures, full mip chain + BC7 at the reference's
+Quality_Normal), sharded per texture with no collective: every rank (= GPU) owns 64 textures per
+step, so 8 GPUs process the config's whole 512-texture set in one step ("scaling": "weak").
+Mpix = level-0 pixels; every texture additionally carries its 11 smaller levels.
+
+One "step" = one pass of the hot path over the rank's batch:
+  value : inputs already resident in HBM, rosy_tex_encode_device() per texture on one stream,
+          timed with CUDA events on that stream (barrier + synchronize both sides, max over ranks)
+  e2e   : the same batch through the reference-facing C ABI with HOST buffers
+          (rosy_tex_submit_rgba8 + rosy_tex_wait_all: pinned H2D, kernels, D2H of the .dds bytes),
+          timed by the host clock around the calls, max over ranks
+  roofline     : per-kernel CUDA-event durations taken inside the timed region
+  cpu_baseline : the CPU oracle (oracle/, "port" - NVTT itself is closed source and absent) on a
+                 bounded sample of the same textures, all host cores, rank 0 at N = 1 only
+
+`--impl reference` times that CPU oracle as the reference arm (the only CPU implementation of the
+path that exists here).  The product path never touches oracle/.
+"""
+import argparse
+import ctypes as C
+import hashlib
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "BC7+mips Mpix/s"
+UNIT = "Mpix/s"
+SM_COUNT = 148
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--textures", type=int, default=64, help="textures per GPU per step")
+    ap.add_argument("--size", type=int, default=2048)
+    ap.add_argument("--quality", default="normal", choices=["fast", "normal", "high"])
+    ap.add_argument("--kind", default="albedo", choices=["albedo", "normal", "metal_rough"])
+    ap.add_argument("--format", default="bc7", choices=["bc7", "bc5", "bc4"])
+    ap.add_argument("--cpu-sample", type=int, default=2, help="textures in the cpu_baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------ inputs
+def make_textures(kind, size, count, rank):
+    """`count` distinct synthetic textures (SURVEY.md 8d generators).  A few seeded bases are
+    generated with the full noise stack; the rest are cheap re-arrangements of them (odd rolls,
+    flips, transposes, channel rotations), which keeps start-up at seconds while every texture
+    still has different 4x4 blocks."""
+    from rosy_b200 import synth
+
+    nbase = min(count, 4)
+    bases = [synth.make(kind, size, size, 16 * rank + i) for i in range(nbase)]
+    out = []
+    for i in range(count):
+        b = bases[i % nbase]
+        v = i // nbase
+        if v:
+            b = np.roll(b, (37 * v + 1, 53 * v + 3), axis=(0, 1))
+            if v & 1:
+                b = b[::-1]
+            if v & 2:
+                b = b[:, ::-1]
+            if v & 4:
+                b = b.transpose(1, 0, 2)
+            if kind == "albedo" and v >= 8:
+                b = b[..., [(0 + v) % 3, (1 + v) % 3, (2 + v) % 3, 3]]
+        out.append(np.ascontiguousarray(b))
+    return out
+
+
+# ------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """SM clock + throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    REASONS = {
+        0x8: "hw_slowdown",
+        0x40: "hw_thermal_slowdown",
+        0x20: "sw_thermal_slowdown",
+        0x4: "sw_power_cap",
+        0x80: "hw_power_brake_slowdown",
+    }
+
+    def __init__(self, torch, device_index):
+        self.samples, self.reasons, self.sm_max = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._stop.clear()
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join()
+            self._thread = None
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": 0}
+        return {
+            "sm_mhz": float(np.median(self.samples)),
+            "sm_max_mhz": self.sm_max,
+            "reasons": sorted(self.reasons),
+            "samples": len(self.samples),
+        }
+
+
+# ------------------------------------------------------------------------------------ cpu legs
+def cpu_oracle_run(textures, kind, fmt, quality, threads=0):
+    """One pass of the CPU oracle over `textures`; returns seconds."""
+    import oracle as O
+
+    okind = O.KIND_NORMAL if kind == "normal" else O.KIND_SRGB
+    t0 = time.perf_counter()
+    for img in textures:
+        O.generate_texture(img, okind, fmt, quality, threads=threads)
+    return time.perf_counter() - t0
+
+
+def run_reference_arm(args, rank):
+    """--impl reference: the CPU implementation of the path on this box's host cores.
+
+    NVTT 3.2.5 (what the reference links, src/premake5.lua:123) is a closed-source Windows DLL that
+    is neither in /root/reference nor in this image, so the reference's own CPU code for the path
+    cannot be built; the timed CPU arm is the oracle port (oracle/, kind = "port")."""
+    if rank != 0:
+        return
+    import oracle as O
+
+    fmt = {"bc7": 0, "bc5": 1, "bc4": 2}[args.format]
+    q = {"fast": 0, "normal": 1, "high": 2}[args.quality]
+    sample = make_textures(args.kind, args.size, 1, 0)
+    cores = O.max_threads()
+    for _ in range(max(1, min(args.warmup, 1))):
+        cpu_oracle_run(sample, args.kind, fmt, q)
+    times = [cpu_oracle_run(sample, args.kind, fmt, q) for _ in range(args.steps)]
+    sec = float(np.mean(times))
+    mpix = len(sample) * args.size * args.size / 1e6
+    value = mpix / sec
+    line = {
+        "impl": "reference",
+        "metric": METRIC,
+        "value": value,
+        "unit": UNIT,
+        "n_gpus": args.gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": sec * 1e3,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "u8+fp32",
+        "data": "synthetic",
+        "config": workload_config(args, args.textures),
+        "cpu_baseline": {
+            "value": value,
+            "unit": UNIT,
+            "cores": cores,
+            "kind": "port",
+            "sample": f"1 x {args.size}x{args.size} {args.kind}, full mips + {args.format.upper()} {args.quality}, per step",
+        },
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, ntex, note=None):
+    c = {
+        "workload": f"configs[4] throughput sweep: {args.size}x{args.size} synthetic {args.kind}, full mip chain + "
+        f"{args.format.upper()} at quality {args.quality}, sharded per texture "
+        f"({args.textures} textures per GPU per step; 8 GPUs = the config's 512)",
+        "textures_per_gpu": ntex,
+        "size": args.size,
+        "format": args.format,
+        "quality": args.quality,
+        "parallelism": f"texture-sharded x{args.gpus}, no collective",
+        "l2": "inputs per step exceed the 126 MB L2 (no flush needed)"
+        if ntex * args.size * args.size * 4 > L2_BYTES
+        else "L2 flushed between steps",
+    }
+    if note:
+        c["note"] = note
+    return c
+
+
+# ------------------------------------------------------------------------------------ main
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from rosy_b200 import texture as T
+
+    T.lib()  # fails loudly when the CUDA extension is missing
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    fmt = {"bc7": T.FORMAT_BC7, "bc5": T.FORMAT_BC5, "bc4": T.FORMAT_BC4}[args.format]
+    q = {"fast": 0, "normal": 1, "high": 2}[args.quality]
+    kind = {"albedo": T.KIND_COLOR, "normal": T.KIND_NORMAL_MAP, "metal_rough": T.KIND_METALLIC_ROUGHNESS}[args.kind]
+    T.init(devices=[local_rank], quality=q)
+
+    n, size = args.textures, args.size
+    textures = make_textures(args.kind, size, n, rank)
+    d = T.desc(size, size, kind, fmt, q, -1)
+    in_bytes = size * size * 4
+    dds_bytes = T.dds_size(d)
+    blk_bytes = dds_bytes - T.DDS_HEADER_BYTES
+    chain_bytes = T.chain_size(size, size)
+    mpix_step = n * size * size / 1e6
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- device-resident leg: `value` + per-kernel durations --------------------
+    d_in = torch.empty((n, in_bytes), dtype=torch.uint8, device=dev)
+    for i, img in enumerate(textures):
+        d_in[i].copy_(torch.from_numpy(img.reshape(-1)))
+    d_chain = torch.empty(chain_bytes, dtype=torch.uint8, device=dev)
+    d_scratch = torch.zeros(T.device_scratch_size(d), dtype=torch.uint8, device=dev)
+    d_blocks = torch.empty((n, blk_bytes), dtype=torch.uint8, device=dev)
+    flush = None
+    if n * in_bytes <= L2_BYTES:
+        flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step(events=None):
+        if flush is not None:
+            flush.fill_(1)
+        for i in range(n):
+            if events is not None:
+                ea, eb, ec = events[i]
+                ea.record()
+            T.mips_device(d, d_in[i].data_ptr(), d_chain.data_ptr(), d_scratch.data_ptr(), stream)
+            if events is not None:
+                eb.record()
+            T.blocks_device(d, d_in[i].data_ptr(), d_chain.data_ptr(), d_blocks[i].data_ptr(), stream)
+            if events is not None:
+                ec.record()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    clocks = ClockSampler(torch, local_rank)
+    kernel_events = [
+        [tuple(torch.cuda.Event(enable_timing=True) for _ in range(3)) for _ in range(n)] for _ in range(args.steps)
+    ]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = T.kernel_launches()
+    clocks.start()
+    barrier()
+    e0.record()
+    for k in range(args.steps):
+        step(kernel_events[k])
+    e1.record()
+    barrier()
+    clocks.stop()
+    launches = T.kernel_launches() - launches0
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_step = ms_total / args.steps
+    value = world * mpix_step / (ms_step * 1e-3)
+    mip_ms = float(np.mean([ea.elapsed_time(eb) for evs in kernel_events for (ea, eb, ec) in evs]))
+    enc_ms = float(np.mean([eb.elapsed_time(ec) for evs in kernel_events for (ea, eb, ec) in evs]))
+    clk = clocks.summary()
+
+    # ---------------- e2e leg: host buffers through the C ABI work queue --------------------
+    e2e = None
+    if not args.no_e2e:
+        L = T.lib()
+        host_in = [L.rosy_tex_alloc_host(in_bytes) for _ in range(n)]
+        host_out = [L.rosy_tex_alloc_host(dds_bytes) for _ in range(n)]
+        if not all(host_in) or not all(host_out):
+            raise SystemExit("bench.py: pinned host allocation failed")
+        for p, img in zip(host_in, textures):
+            C.memmove(p, img.ctypes.data, in_bytes)
+        lens = [C.c_size_t() for _ in range(n)]
+
+        def e2e_step():
+            for i in range(n):
+                rc = L.rosy_tex_submit_rgba8(C.byref(d), host_in[i], host_out[i], dds_bytes, C.byref(lens[i]))
+                if rc:
+                    raise SystemExit(f"rosy_tex_submit_rgba8 failed: {L.rosy_tex_last_error().decode()}")
+            rc = L.rosy_tex_wait_all()
+            if rc:
+                raise SystemExit(f"rosy_tex_wait_all failed: {L.rosy_tex_last_error().decode()}")
+            # device->host read of the step's result: the first bytes of the last .dds (already in host memory)
+            return C.string_at(host_out[n - 1], 4)
+
+        for _ in range(max(1, min(args.warmup, 2))):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            magic = e2e_step()
+        torch.cuda.synchronize()
+        sec = time.perf_counter() - t0
+        barrier()
+        assert magic == b"DDS ", magic
+        # the e2e output must be the same bytes as the device-resident leg produced
+        got = np.ctypeslib.as_array(C.cast(host_out[0], C.POINTER(C.c_uint8)), shape=(dds_bytes,))
+        assert (got[T.DDS_HEADER_BYTES:] == d_blocks[0].cpu().numpy()).all(), "e2e and device legs disagree"
+        sec = max_over_ranks(sec)
+        e2e = {
+            "value": world * mpix_step * args.steps / sec,
+            "unit": UNIT,
+            "h2d_bytes_per_step": n * in_bytes,
+            "d2h_bytes_per_step": n * blk_bytes,
+            "ms_per_step": sec * 1e3 / args.steps,
+            "api": "rosy_tex_submit_rgba8 + rosy_tex_wait_all (pinned host buffers, 2 slots per device)",
+        }
+        for p in host_in + host_out:
+            L.rosy_tex_free_host(p)
+
+    # ---------------- roofline of the dominant kernel ----------------------------------------
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    npx = size * size
+    # algorithmic bytes per launch: mip kernel 4N + 4N/3 (+4N for normal maps, whose level 0
+    # is rewritten); encoders read 4 B/px and write 1 (BC7/BC5) or 0.5 (BC4) B/px over 4N/3 px
+    chain_px = chain_bytes // 4
+    mip_bytes = 4 * npx + 4 * (chain_px - npx) + (4 * npx if kind == T.KIND_NORMAL_MAP else 0)
+    enc_bytes = 4 * chain_px + blk_bytes
+    mip_gbs = mip_bytes / (mip_ms * 1e-3) / 1e9
+    enc_gbs = enc_bytes / (enc_ms * 1e-3) / 1e9
+    prof = load_profile_counts(args)
+    sm_mhz = clk["sm_mhz"] or float(peaks.get("sm_max_mhz", 1965.0))
+    issue_peak = SM_COUNT * 4 * sm_mhz * 1e6 / 1e9  # G warp-instructions / s at the clock seen under load
+    enc_kernel = "bc7_encode_kernel" if fmt == T.FORMAT_BC7 else "bc45_encode_kernel"
+    if fmt == T.FORMAT_BC7:
+        roofline = {
+            "kernel": enc_kernel,
+            "bound": "issue",
+            "achieved": None,
+            "peak": issue_peak,
+            "unit": "Gwarp-inst/s",
+            "frac": None,
+            "traffic": prof.get("bc7_dram_bytes_per_launch"),
+            "ms_per_launch": enc_ms,
+            "share_of_step": enc_ms * n / ms_step,
+            "hbm": {"achieved": enc_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": enc_gbs / hbm_peak,
+                    "algorithmic_bytes_per_launch": enc_bytes, "peak_source": peak_src},
+            "note": "BC7 is issue-slot bound (north_star): achieved = ncu smsp__inst_executed.sum per launch "
+            "(profiles/) / live CUDA-event duration; peak = 148 SMs x 4 schedulers x SM clock under load",
+        }
+        if prof.get("bc7_warp_inst_per_launch"):
+            a = prof["bc7_warp_inst_per_launch"] / (enc_ms * 1e-3) / 1e9
+            roofline["achieved"] = a
+            roofline["frac"] = a / issue_peak
+            roofline["inst_source"] = prof.get("source")
+    else:
+        roofline = {
+            "kernel": enc_kernel, "bound": "hbm", "achieved": enc_gbs, "peak": hbm_peak, "unit": "GB/s",
+            "frac": enc_gbs / hbm_peak, "traffic": None, "ms_per_launch": enc_ms,
+            "share_of_step": enc_ms * n / ms_step, "algorithmic_bytes_per_launch": enc_bytes,
+            "peak_source": peak_src,
+        }
+    roofline_mip = {
+        "kernel": "mip_fused_kernel", "bound": "hbm", "achieved": mip_gbs, "peak": hbm_peak, "unit": "GB/s",
+        "frac": mip_gbs / hbm_peak, "traffic": prof.get("mip_dram_bytes_per_launch"), "ms_per_launch": mip_ms,
+        "share_of_step": mip_ms * n / ms_step, "algorithmic_bytes_per_launch": mip_bytes, "peak_source": peak_src,
+    }
+
+    # ---------------- cpu_baseline (rank 0, N = 1 only) ----------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle as O
+
+        sample = textures[: max(1, args.cpu_sample)]
+        sec = cpu_oracle_run(sample, args.kind, fmt, q)
+        cpu = {
+            "value": len(sample) * npx / 1e6 / sec,
+            "unit": UNIT,
+            "cores": O.max_threads(),
+            "kind": "port",
+            "sample": f"{len(sample)} of the step's {n} textures ({size}x{size} {args.kind}, full mips + "
+            f"{args.format.upper()} {args.quality}), {sec:.1f} s of CPU work",
+        }
+
+    if rank == 0:
+        line = {
+            "metric": METRIC,
+            "value": value,
+            "unit": UNIT,
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": max(3, args.warmup),
+            "ms_per_step": ms_step,
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": None,
+            "dtype": "u8+fp32",
+            "data": "synthetic",
+            "config": workload_config(args, n),
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "roofline_mip": roofline_mip,
+            "cpu_baseline": cpu,
+            "clocks": clk,
+            "mpix_all_levels_per_step": n * chain_px / 1e6,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    T.shutdown()
+
+
+def load_profile_counts(args):
+    """ncu-derived per-launch counts for the bench workload (profiles/bench_counts.json), valid only
+    for the kernel source they were captured from."""
+    path = os.path.join(ROOT, "profiles", "bench_counts.json")
+    try:
+        with open(path) as f:
+            doc = json.load(f)
+    except Exception:
+        return {}
+    key = f"{args.kind}-{args.size}-{args.format}-{args.quality}"
+    ent = doc.get(key)
+    if not ent:
+        return {}
+    src = os.path.join(ROOT, "rosy_b200", "csrc", "bc7_encode.cu")
+    with open(src, "rb") as f:
+        sha = hashlib.sha256(f.read()).hexdigest()[:16]
+    if ent.get("bc7_source_sha") and ent["bc7_source_sha"] != sha:
+        ent = dict(ent)
+        ent.pop("bc7_warp_inst_per_launch", None)  # stale: counted on another version of the kernel
+    return ent
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,162 @@
+"""CPU suite, part 1: the oracle is pinned against every vector that is NOT ours.
+
+  * BC4/BC5 encoder  == the reference's vendored stb_dxt.h (golden vectors; live oracle/_ref when built)
+  * BC7/BC4 decoder  == Pillow's independent BCn decoder (golden vectors; live Pillow as well)
+  * DDS container    == what the reference's own dds::readImage parses (golden; live oracle/_ref)
+  * colour mip model ~  stb_image_resize2's sRGB box filter, the reference tree's other statement of
+                        "sRGB-correct alpha-weighted box" (sanity bound, it quantises differently)
+NVTT itself is closed source, so the BC7 *encoder's* choices and NVTT's exact filter arithmetic stay
+unpinned.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_bc4_bc5_encoder_matches_reference_stb_dxt_vectors(oracle):
+    g = np.load(os.path.join(GOLD, "bc45_stb_dxt.npz"))
+    for s, want in zip(g["bc4_src"], g["bc4_blocks"]):
+        assert (oracle.bc4_encode_block(s) == want).all(), s
+    for s, want in zip(g["bc5_src"], g["bc5_blocks"]):
+        assert (oracle.bc5_encode_block(s) == want).all()
+
+
+def test_bc4_bc5_encoder_matches_live_reference(oracle):
+    if not oracle.have_ref_stb():
+        pytest.skip("oracle/_ref not built on this box (needs /root/reference)")
+    rng = np.random.default_rng(11)
+    for _ in range(2000):
+        spread = int(rng.integers(1, 256))
+        s = np.clip(int(rng.integers(0, 256)) + rng.integers(-spread, spread + 1, 16), 0, 255).astype(np.uint8)
+        assert (oracle.bc4_encode_block(s) == oracle.ref_bc4_block(s)).all(), s
+    rg = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    for s in rg:
+        assert (oracle.bc5_encode_block(s) == oracle.ref_bc5_block(s)).all()
+
+
+def test_bc7_decoder_matches_pillow_vectors(oracle):
+    g = np.load(os.path.join(GOLD, "bcn_decode_pillow.npz"))
+    blocks = g["bc7_blocks"]
+    modes = oracle.bc7_block_modes(blocks)
+    assert set(modes.tolist()) == set(range(8)), "vectors must cover every BC7 mode"
+    got = oracle.decode_image(blocks.reshape(-1), 256, 256)
+    assert (got == g["bc7_rgba"]).all()
+    got4 = oracle.decode_image(g["bc4_blocks"].reshape(-1), 128, 128, oracle.FMT_BC4)
+    assert (got4[..., 0] == g["bc4_l"]).all()
+
+
+def test_bc7_encoder_output_decodes_identically_in_pillow(oracle, synth):
+    """every block the oracle's encoder emits is a valid block an independent decoder reads the same"""
+    from PIL import Image
+
+    for name, idx in [("albedo", 7), ("random", 3), ("normal", 1)]:
+        img = synth.make(name, 64, 64, idx)
+        for q in (0, 1, 2):
+            blocks = oracle.encode_image(img, oracle.FMT_BC7, q)
+            assert (oracle.bc7_block_modes(blocks) >= 0).all()
+            pil = np.array(Image.frombytes("RGBA", (64, 64), blocks.tobytes(), "bcn", 7))
+            assert (pil == oracle.decode_image(blocks, 64, 64)).all()
+
+
+def test_dds_header_vectors_and_reference_reader(oracle):
+    with open(os.path.join(GOLD, "dds_reader.json")) as f:
+        cases = json.load(f)
+    assert len(cases) >= 20
+    for c in cases:
+        w, h, fmt = c["w"], c["h"], c["fmt"]
+        hdr = oracle.dds_header(w, h, oracle.count_mipmaps(w, h), fmt)
+        assert bytes(hdr).hex() == c["header_hex"]
+        assert oracle.dds_size(w, h, fmt) == c["size"]
+        p = c["parsed"]  # what the Engine's reader (dds.hpp:409-574) made of it
+        assert p["numMips"] == oracle.count_mipmaps(w, h) and p["width"] == w and p["height"] == h
+        assert p["format"] == {0: 98, 1: 83, 2: 80}[fmt] and p["arraySize"] == 1 and p["dimension"] == 3
+        off = 148
+        bb = 8 if fmt == oracle.FMT_BC4 else 16
+        for l, (o, n) in enumerate(p["mips"][: p["numMips"]]):
+            lw, lh = oracle.level_extent(w, h, l)
+            assert o == off and n == ((lw + 3) // 4) * ((lh + 3) // 4) * bb, (w, h, l)
+            off += n
+        assert off == c["size"], "the file must hold every level (reader does no bounds check)"
+        if oracle.have_ref_dds():
+            data = np.zeros(c["size"], dtype=np.uint8)
+            data[:148] = hdr
+            live = oracle.ref_dds_read(data)
+                live["mips"] = [list(m) for m in live["mips"]]
+                assert live == p
+
+
+def test_colour_mip_level1_close_to_stb_image_resize(oracle):
+    g = np.load(os.path.join(GOLD, "stbir_srgb_box.npz"))
+    for key in ("a", "o"):
+        img, want = g["in_" + key], g["out_" + key]
+        got = oracle.mip_chain(img, oracle.KIND_SRGB)[1]
+        assert got.shape == want.shape
+        # alpha is filtered identically (plain box); colour agrees where any texel is visible
+        d = np.abs(got.astype(int) - want.astype(int))
+        assert d[..., 3].max() <= 1
+        vis = want[..., 3] > 8
+        assert d[vis][:, :3].max() <= 2, d[vis][:, :3].max()
+
+
+def test_mip_geometry(oracle):
+    for (w, h, n) in [(1024, 1024, 11), (2048, 2048, 12), (4096, 4096, 13), (8192, 8192, 14), (1, 1, 1), (5, 3, 3), (256, 64, 9)]:
+        assert oracle.count_mipmaps(w, h) == n
+    assert oracle.chain_pixels(1024, 1024) == 1398101 and oracle.chain_blocks(1024, 1024) == 87383
+    assert oracle.chain_blocks(4096, 4096) == 1398103 and oracle.dds_size(4096, 4096, 0) == 22369796
+    assert oracle.chain_blocks(8192, 8192) == 5592407 and oracle.dds_size(2048, 2048, 0) == 5592580
+    assert oracle.level_extent(5, 3, 1) == (2, 1) and oracle.level_extent(5, 3, 2) == (1, 1)
+
+
+def test_mip_known_answers(oracle, synth):
+    for l in oracle.mip_chain(synth.constant(64, 32, (187, 187, 187, 255)), oracle.KIND_SRGB):
+        assert (l == np.array([187, 187, 187, 255], dtype=np.uint8)).all()
+    for l in oracle.mip_chain(synth.constant(32, 32, (128, 128, 255, 255)), oracle.KIND_NORMAL):
+        assert (l == np.array([128, 128, 255, 255], dtype=np.uint8)).all()
+    lv = oracle.mip_chain(synth.constant(16, 16, (200, 10, 10, 0)), oracle.KIND_SRGB)
+    assert (lv[0] == np.array([200, 10, 10, 0], dtype=np.uint8)).all() and (lv[1] == 0).all()
+    # a black/white checker averages in LINEAR light: 0.5 linear = 188 sRGB, not 128
+    chk = np.zeros((8, 8, 4), dtype=np.uint8)
+    chk[..., 3] = 255
+    chk[::2, ::2, :3] = 255
+    chk[1::2, 1::2, :3] = 255
+    assert (oracle.mip_chain(chk, oracle.KIND_SRGB)[1][..., :3] == 188).all()
+    # normal maps: level k = normalise(box^k(level 0)); a tilted pair renormalises to unit length
+    nm = synth.normal(64, 64, 1)
+    for l in oracle.mip_chain(nm, oracle.KIND_NORMAL)[:5]:
+        v = l[..., :3].astype(np.float64) / 255.0 * 2.0 - 1.0
+        assert np.abs(np.linalg.norm(v, axis=-1) - 1.0).max() < 0.02
+    off = oracle.mip_chain(nm, oracle.KIND_NORMAL, oracle.NORMALIZE_OFF)
+    assert (off[0] == nm).all()
+
+
+def test_bc7_encoder_known_answers_and_quality_order(oracle, synth):
+    rng = np.random.default_rng(5)
+    for _ in range(64):  # solid blocks decode exactly
+        c = rng.integers(0, 256, 4)
+        px = np.tile(c.astype(np.uint8), (16, 1))
+        assert (oracle.bc7_decode_block(oracle.bc7_encode_block(px, 1)) == px).all()
+    img = synth.albedo(128, 128, 0)
+    p = [oracle.psnr(img, oracle.decode_image(oracle.encode_image(img, 0, q), 128, 128)) for q in (0, 1, 2)]
+    assert p[0] <= p[1] + 1e-9 <= p[2] + 2e-9 and p[1] > 40.0, p
+    cut = synth.albedo(128, 128, 7)
+    pc = oracle.psnr(cut, oracle.decode_image(oracle.encode_image(cut, 0, 1), 128, 128))
+    assert pc > 38.0, pc
+
+
+def test_whole_stage_layout(oracle, synth):
+    img = synth.albedo(64, 32, 0)
+    dds = oracle.generate_texture(img, oracle.KIND_SRGB)
+    assert dds.size == oracle.dds_size(64, 32, 0)
+    assert bytes(dds[:4]) == b"DDS " and int.from_bytes(bytes(dds[128:132]), "little") == 98
+    chain = oracle.mip_chain(img, oracle.KIND_SRGB)
+    off = 148
+    for lvl in chain:
+        lh, lw = lvl.shape[:2]
+        n = ((lw + 3) // 4) * ((lh + 3) // 4) * 16
+        assert (dds[off : off + n] == oracle.encode_image(lvl, 0, 1)).all()
+        off += n
+    assert off == dds.size
