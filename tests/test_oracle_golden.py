@@ -85,8 +85,8 @@ def test_dds_header_vectors_and_reference_reader(oracle):
             data = np.zeros(c["size"], dtype=np.uint8)
             data[:148] = hdr
             live = oracle.ref_dds_read(data)
-                live["mips"] = [list(m) for m in live["mips"]]
-                assert live == p
+            live["mips"] = [list(m) for m in live["mips"]]
+            assert live == p
 
 
 def test_colour_mip_level1_close_to_stb_image_resize(oracle):
