@@ -3,19 +3,25 @@
 // Replaces nvtt::Context::compress(..., Format_BC7) at /root/reference/src/Packager/Packager.cpp:245
 // (colour maps) and :296 (normal maps).  One launch encodes the blocks of every mip level.
 //
-// Mapping: one 4x4 block per thread.  The 16 texels live in shared memory, transposed
-// ([texel][thread], conflict free), so that every search loop is rolled over texels while the
-// palette of the candidate end-point pair lives in registers.  All decisions are taken on
-// integer sums of squared differences:
+// Mapping: one 4x4 block per thread; the kernel is instruction-issue bound, so the design goals
+// are (a) few instructions per fit and (b) a small instruction footprint (the first version of this
+// kernel was 172 KB of SASS against a 32 KB L1.5 instruction cache and stalled on fetch).
+//   * The search is a warp-uniform JOB LIST held in constant memory ("fit subset k of partition
+//     #i of mode m", "rank the partitions", ...) walked by one loop, so every piece of code - the
+//     three `prepare<NC>` and three `refine<IB>` instances, the estimator, the packer - exists once.
+//   * Per-thread state lives in shared memory columns [field][thread] (conflict free, no barrier
+//     is ever needed because a thread only touches its own column): the 16 texels, the same
+//     texels as byte planes (channel c of texels 4k..4k+3 in one word), the cached all-texel
+//     RGB fit, the chosen partitions and the best solution so far.  No local memory is used.
+//   * All subset statistics are integer dot products of byte planes against byte masks (dp4a):
+//     moments for the PCA, and the least-squares sums from per-texel weight bytes that one PRMT
+//     looks up from the index nibbles.
 //   * index search: exhaustive, 3 integer instructions per (texel, palette entry):
 //         dot = dp4a(texel, entry);  key = K[entry] - 32*dot;  best = min(best, key)
-//     with K = (|entry|^2 << 4) | entry_index, so one signed min yields both error and index;
-//   * subset moments for the PCA: integer, exact; converted to fp32 only for the 4 power iterations;
-//   * partition ranking: per-partition integer moments from byte-planar texels with dp4a against
-//     0xFF byte masks, then a line-fit residual estimate in fp32.
-// fp32 expression order is part of the specification ("spec v1", DESIGN.md): this file is built
-// with -fmad=false and uses IEEE division / sqrt, so its decisions coincide with the scalar
-// statement in oracle/bc7.c (which the tests use as the checker; nothing here includes it).
+//     with K = (|entry|^2 << 4) | entry_index, so one signed min yields both error and index.
+// fp32 expression order is part of the specification ("spec v1", DESIGN.md 4.2): this file is built
+// with -fmad=false and IEEE division / sqrt, so its decisions coincide with the scalar statement
+// in oracle/bc7.c (which the tests use as the checker; nothing here includes it).
 //
 // Tensor cores are not used: there is no dense contraction anywhere in the search.
 #include <cuda_runtime.h>
@@ -27,19 +33,50 @@
 namespace rosy_tex {
 namespace {
 
-constexpr int NT = 128;  // threads (= blocks) per CTA
-constexpr int TOPK = 6;  // most partitions refined per mode (high tier)
+constexpr int NT = 128;   // threads (= blocks) per CTA
+constexpr int TOPK = 6;   // most partitions refined per mode (high tier)
+constexpr int MAXJOBS = 96;
 
 __constant__ uint8_t c_SOLID5[256][2];       // best 7-bit end-point pair for a solid value (mode 5)
 __constant__ uint32_t c_PART2_BYTES[64][4];  // 0xFF per texel of subset 1, texels 4k..4k+3 in word k
 __constant__ uint32_t c_PART3_BYTES[64][2][4];
-__device__ uint16_t g_P3M1[64], g_P3M2[64];  // 3-subset partitions as 16-bit masks of subsets 1, 2
-__device__ uint16_t g_P2M[64];
-__device__ uint8_t g_ANCHOR2[64], g_ANCHOR3A[64], g_ANCHOR3B[64];
+__constant__ uint16_t c_P3M1[64], c_P3M2[64];  // 3-subset partitions as 16-bit masks of subsets 1, 2
+__constant__ uint8_t c_ANCHOR2[64], c_ANCHOR3A[64], c_ANCHOR3B[64];
+__constant__ uint2 c_JOBS[3][MAXJOBS];       // per quality tier
+__constant__ int c_NJOBS[3];
+
+// ---- job encoding (built on the host, bc7_upload_tables) ---------------------------------------
+enum { JOB_PREP_P3 = 0, JOB_FIT = 1, JOB_EST = 2 };
+enum { PB_NONE = 0, PB_SHARED = 1, PB_PER_EP = 2 };
+enum { PREP_COMPUTE = 0, PREP_FROM_P3 = 1, PREP_MODE6 = 2 };
+enum { AREQ_ANY = 0, AREQ_OPAQUE = 1, AREQ_ALPHA = 2 };
+enum { DEST_PART = 0, DEST_COLOUR = 1, DEST_SCALAR = 2 };
+// views: 0 RGBA, 1 RGB, 2..4 colour of rotation 1..3, 5..8 scalar of rotation 0..3
+//   sel   = __byte_perm selector producing the view's texel (unused bytes zero)
+//   pcmap = physical byte plane of logical channel c in nibble c
+__constant__ uint32_t c_VIEW_SEL[9] = {0x3210u, 0x4210u, 0x4213u, 0x4230u, 0x4310u,
+                                       0x4443u, 0x4440u, 0x4441u, 0x4442u};
+__constant__ uint32_t c_VIEW_PC[9] = {0x3210u, 0x0210u, 0x0213u, 0x0230u, 0x0310u,
+                                      0x0003u, 0x0000u, 0x0001u, 0x0002u};
+// w0: type[0:2] mode[2:5] ns[5:7] k[7:9] prow[9:15] view[15:19] nc[19:22] ib[22:25] bits[25:29] pbmode[29:31]
+// w1: prep[0:2] first[2] last[3] areq[4:6] dest[6:8] idxsel[8] rot[9:11] estkind[11:13]
+struct JobFields {
+    int type, mode, ns, k, prow, view, nc, ib, bits, pbmode, prep, first, last, areq, dest, idxsel, rot, estkind;
+};
+inline uint2 pack_job(const JobFields& j) {
+    uint2 w;
+    w.x = (uint32_t)j.type | (uint32_t)j.mode << 2 | (uint32_t)j.ns << 5 | (uint32_t)j.k << 7 |
+          (uint32_t)j.prow << 9 | (uint32_t)j.view << 15 | (uint32_t)j.nc << 19 | (uint32_t)j.ib << 22 |
+          (uint32_t)j.bits << 25 | (uint32_t)j.pbmode << 29;
+    w.y = (uint32_t)j.prep | (uint32_t)j.first << 2 | (uint32_t)j.last << 3 | (uint32_t)j.areq << 4 |
+          (uint32_t)j.dest << 6 | (uint32_t)j.idxsel << 8 | (uint32_t)j.rot << 9 | (uint32_t)j.estkind << 11;
+    return w;
+}
 
 struct Params {
     Chain chain;
-    Bc7Tier tier;
+    int tier;               // 0 fast, 1 normal, 2 high: selects the job list
+    int ls_rounds, pb_search;
     const uint8_t* level0;  // level 0 pixels (colour maps: the input image itself)
     const uint8_t* chainbuf;
     uint8_t* out;
@@ -49,21 +86,20 @@ struct Params {
     uint64_t num_blocks;
 };
 
-enum { PB_NONE = 0, PB_SHARED = 1, PB_PER_EP = 2 };
+// per-thread state columns
+struct Shared {
+    uint32_t px[16][NT];   // texels, RGBA8
+    uint32_t pl[16][NT];   // byte planes: [4*c + k] = channel c of texels 4k..4k+3
+    uint32_t p3[12][NT];   // all-texel RGB prepare: lo[4], hi[4] (float bits), S1[4]
+    uint32_t best[12][NT]; // q[3][2], pb, idx lo/hi, idx2 lo/hi, meta
+    uint8_t parts[5 * TOPK][NT];  // chosen partitions: lists l1, l3, l0, l2, l7
+};
 
 struct Fit {
     uint32_t q0, q1;  // end-point fields, one byte per channel
     uint32_t pb;      // bit 0 / bit 1: p-bit of end point 0 / 1
     uint64_t idx;     // 4 bits per texel (only texels of the subset are non-zero)
     uint32_t err;
-};
-
-struct Solution {
-    uint32_t q[3][2];
-    uint32_t pb;  // bit 2k+e
-    uint64_t idx, idx2;
-    uint32_t err;
-    int mode, partition, rotation, idxsel;
 };
 
 __device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
@@ -74,43 +110,131 @@ template <int IB>
 __device__ __forceinline__ int weight_of(int j) {
     return IB == 2 ? (j * 85 + 2) >> 2 : (IB == 3 ? (j * 73 + 4) >> 3 : (j * 68 + 8) >> 4);
 }
-__device__ __forceinline__ int weight_rt(int ib, int j) {
-    return ib == 2 ? (j * 85 + 2) >> 2 : (ib == 3 ? (j * 73 + 4) >> 3 : (j * 68 + 8) >> 4);
-}
 
 __device__ __forceinline__ int expand_bits(int v, int bits) {
     return bits >= 8 ? v : ((v << (8 - bits)) | (v >> (2 * bits - 8)));
-}
-
-__device__ __forceinline__ int quant_pbit(float x, int bits, int p) {
-    const int tb = bits + 1;
-    float y = x * ((float)((1 << tb) - 1) / 255.0f);
-    int q = (int)floorf((y - (float)p) * 0.5f + 0.5f);
-    return min(max(q, 0), (1 << bits) - 1);
-}
-
-__device__ __forceinline__ int quant_plain(float x, int bits) {
-    int q = (int)floorf(x * ((float)((1 << bits) - 1) / 255.0f) + 0.5f);
-    return min(max(q, 0), (1 << bits) - 1);
 }
 
 __device__ __forceinline__ float clampf(float x, float lo, float hi) {
     return x < lo ? lo : (x > hi ? hi : x);
 }
 
-// The texel view of a fit: byte permutation (channel rotation / scalar extraction) + byte mask.
-struct View {
-    uint32_t sel, msk;
-};
-__device__ __forceinline__ uint32_t fetch(const uint32_t (*spx)[NT], int i, int tid, View v) {
-    return __byte_perm(spx[i][tid], 0u, v.sel) & v.msk;
+// 4 mask bits -> 4 byte masks
+__device__ __forceinline__ uint32_t nibble_to_bytes(uint32_t nib) {
+    return ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
 }
+
+// ---- prepare: integer moments -> principal axis -> extremes along the axis (spec v1 steps 1-3) ----
+struct Prep {
+    float lo[4], hi[4];
+    int S1[4];
+    int n;
+};
+
+template <int NC>
+__device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, uint32_t pcmap,
+                                        uint32_t mask, Prep& P) {
+    const int n = __popc(mask);
+    int S1[NC], S2[NC][NC];
+#pragma unroll
+    for (int a = 0; a < NC; a++) {
+        S1[a] = 0;
+#pragma unroll
+        for (int b = 0; b < NC; b++) S2[a][b] = 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t mk = nibble_to_bytes((mask >> (4 * k)) & 15u);
+        uint32_t pw[NC];
+#pragma unroll
+        for (int a = 0; a < NC; a++) pw[a] = S.pl[4 * ((pcmap >> (4 * a)) & 15u) + k][tid];
+#pragma unroll
+        for (int a = 0; a < NC; a++) {
+            const uint32_t m = pw[a] & mk;
+            S1[a] = dp4a_uu(m, 0x01010101u, S1[a]);
+#pragma unroll
+            for (int b = a; b < NC; b++) S2[a][b] = dp4a_uu(m, pw[b], S2[a][b]);
+        }
+    }
+    float C[NC][NC];
+#pragma unroll
+    for (int a = 0; a < NC; a++)
+#pragma unroll
+        for (int b = a; b < NC; b++) C[a][b] = C[b][a] = (float)(n * S2[a][b] - S1[a] * S1[b]);
+    // principal axis: 4 power iterations from the covariance column with the largest diagonal
+    float cbest = C[0][0], v[NC];
+#pragma unroll
+    for (int a = 0; a < NC; a++) v[a] = C[a][0];
+#pragma unroll
+    for (int c = 1; c < NC; c++) {
+        if (C[c][c] > cbest) {
+            cbest = C[c][c];
+#pragma unroll
+            for (int a = 0; a < NC; a++) v[a] = C[a][c];
+        }
+    }
+    if (!(cbest > 0.0f)) {
+#pragma unroll
+        for (int a = 0; a < NC; a++) v[a] = 1.0f;
+    }
+#pragma unroll 1
+    for (int it = 0; it < 4; it++) {
+        float t[NC], m = 0.0f;
+#pragma unroll
+        for (int a = 0; a < NC; a++) {
+            float s = 0.0f;
+#pragma unroll
+            for (int b = 0; b < NC; b++) s = s + C[a][b] * v[b];
+            t[a] = s;
+            m = fmaxf(m, fabsf(s));
+        }
+        if (m == 0.0f) break;
+        const float r = 1.0f / m;
+#pragma unroll
+        for (int a = 0; a < NC; a++) v[a] = t[a] * r;
+    }
+    float len2 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < NC; c++) len2 = len2 + v[c] * v[c];
+    const float rl = 1.0f / sqrtf(len2);
+#pragma unroll
+    for (int c = 0; c < NC; c++) v[c] = v[c] * rl;
+    float mean[NC];
+    const float fn = (float)n;
+#pragma unroll
+    for (int c = 0; c < NC; c++) mean[c] = (float)S1[c] / fn;
+    float tmin = 3.0e38f, tmax = -3.0e38f;
+#pragma unroll 4
+    for (int i = 0; i < 16; i++) {
+        const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
+        float t = 0.0f;
+#pragma unroll
+        for (int c = 0; c < NC; c++) t = t + ((float)((p >> (8 * c)) & 255u) - mean[c]) * v[c];
+        if ((mask >> i) & 1u) {
+            tmin = t < tmin ? t : tmin;
+            tmax = t > tmax ? t : tmax;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        if (c < NC) {
+            P.lo[c] = clampf(mean[c] + tmin * v[c], 0.0f, 255.0f);
+            P.hi[c] = clampf(mean[c] + tmax * v[c], 0.0f, 255.0f);
+            P.S1[c] = S1[c];
+        } else {
+            P.lo[c] = P.hi[c] = 0.0f;
+            P.S1[c] = 0;
+        }
+    }
+    P.n = n;
+}
+
+// ---- refine: quantise, exhaustive indices, least-squares rounds (spec v1 steps 4-6) ----------------
 
 // Integer SSD of the subset's texels against the palette of (e0, e1); exhaustive index search.
 template <int IB>
-__device__ __forceinline__ uint32_t evaluate(const uint32_t (*spx)[NT], int tid, View view,
-                                             uint32_t mask, uint32_t e0, uint32_t e1,
-                                             uint64_t& idx_out) {
+__device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t sel, uint32_t mask,
+                                             uint32_t e0, uint32_t e1, uint64_t& idx_out) {
     constexpr int L = 1 << IB;
     uint32_t P[L];
     int K[L];
@@ -128,7 +252,7 @@ __device__ __forceinline__ uint32_t evaluate(const uint32_t (*spx)[NT], int tid,
     uint64_t idx = 0;
 #pragma unroll 2
     for (int i = 0; i < 16; i++) {
-        const uint32_t p = fetch(spx, i, tid, view);
+        const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
         int best = 0x7FFFFFFF;
 #pragma unroll
         for (int j = 0; j < L; j++) best = min(best, K[j] - (dp4a_uu(p, P[j], 0) << 5));
@@ -141,236 +265,156 @@ __device__ __forceinline__ uint32_t evaluate(const uint32_t (*spx)[NT], int tid,
     return total;
 }
 
-// quantise the float end points, choose p-bits, evaluate, keep the best in `best`
+// interpolation weights of 4 texels (index nibbles in the low 16 bits) as 4 bytes
 template <int IB>
-__device__ __forceinline__ void quantise_and_try(const uint32_t (*spx)[NT], int tid, View view,
-                                                 uint32_t mask, int nc, int bits, int pbmode,
-                                                 int pb_search, const float lo[4],
-                                                 const float hi[4], Fit& best) {
-    int ncombo = 1;
-    uint32_t combo0 = 0;  // bit e = p-bit of end point e for combination 0
-    if (pbmode == PB_PER_EP) {
-        if (pb_search) {
-            ncombo = 4;
-        } else {
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                float err0 = 0.0f, err1 = 0.0f;
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    if (c < nc) {
-                        const float x = e ? hi[c] : lo[c];
-                        int q = quant_pbit(x, bits, 0);
-                        float d = (float)expand_bits(q << 1, bits + 1) - x;
-                        err0 = err0 + d * d;
-                        q = quant_pbit(x, bits, 1);
-                        d = (float)expand_bits((q << 1) | 1, bits + 1) - x;
-                        err1 = err1 + d * d;
-                    }
-                }
-                combo0 |= (err1 < err0 ? 1u : 0u) << e;
-            }
-        }
-    } else if (pbmode == PB_SHARED) {
-        if (pb_search) {
-            ncombo = 2;
-        } else {
-            float err0 = 0.0f, err1 = 0.0f;
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    if (c < nc) {
-                        const float x = e ? hi[c] : lo[c];
-                        int q = quant_pbit(x, bits, 0);
-                        float d = (float)expand_bits(q << 1, bits + 1) - x;
-                        err0 = err0 + d * d;
-                    }
-                }
-            }
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    if (c < nc) {
-                        const float x = e ? hi[c] : lo[c];
-                        int q = quant_pbit(x, bits, 1);
-                        float d = (float)expand_bits((q << 1) | 1, bits + 1) - x;
-                        err1 = err1 + d * d;
-                    }
-                }
-            }
-            combo0 = err1 < err0 ? 3u : 0u;
-        }
-    }
-    const uint32_t chmask = nc == 4 ? 0xFFFFFFFFu : (nc == 3 ? 0x00FFFFFFu : 0x000000FFu);
-    for (int k = 0; k < ncombo; k++) {
-        uint32_t pb = combo0;
-        if (ncombo == 4) pb = (uint32_t)k;           // (k & 1, k >> 1)
-        if (ncombo == 2) pb = k ? 3u : 0u;
-        uint32_t q0 = 0, q1 = 0, e0 = 0, e1 = 0;
-#pragma unroll
-        for (int c = 0; c < 4; c++) {
-            int qa, qb, ea, eb;
-            if (pbmode == PB_NONE) {
-                qa = quant_plain(lo[c], bits);
-                qb = quant_plain(hi[c], bits);
-                ea = expand_bits(qa, bits);
-                eb = expand_bits(qb, bits);
-            } else {
-                const int pa = pb & 1, pbb = (pb >> 1) & 1;
-                qa = quant_pbit(lo[c], bits, pa);
-                qb = quant_pbit(hi[c], bits, pbb);
-                ea = expand_bits((qa << 1) | pa, bits + 1);
-                eb = expand_bits((qb << 1) | pbb, bits + 1);
-            }
-            q0 |= (uint32_t)qa << (8 * c);
-            q1 |= (uint32_t)qb << (8 * c);
-            e0 |= (uint32_t)ea << (8 * c);
-            e1 |= (uint32_t)eb << (8 * c);
-        }
-        q0 &= chmask;
-        q1 &= chmask;
-        e0 &= chmask;
-        e1 &= chmask;
-        uint64_t idx;
-        const uint32_t err = evaluate<IB>(spx, tid, view, mask, e0, e1, idx);
-        if (err < best.err) {
-            best.err = err;
-            best.q0 = q0;
-            best.q1 = q1;
-            best.pb = pb;
-            best.idx = idx;
-        }
-    }
+__device__ __forceinline__ uint32_t weight_bytes(uint32_t nib16) {
+    if (IB == 2) return __byte_perm(0x402B1500u, 0u, nib16);                 // 0 21 43 64
+    if (IB == 3) return __byte_perm(0x1B120900u, 0x40372E25u, nib16);        // 0 9 18 27 | 37 46 55 64
+    const uint32_t s = nib16 & 0x7777u;
+    const uint32_t wl = __byte_perm(0x0D090400u, 0x1E1A1511u, s);            // 0 4 9 13 | 17 21 26 30
+    const uint32_t wh = __byte_perm(0x2F2B2622u, 0x403C3733u, s);            // 34 38 43 47 | 51 55 60 64
+    uint32_t h = (nib16 >> 3) & 0x1111u;       // bit 3 of every nibble, at bits 0 4 8 12
+    h = (h | (h << 8)) & 0x00110011u;          // at bits 0 4 16 20
+    h = (h | (h << 4)) & 0x01010101u;          // at bits 0 8 16 24
+    h *= 0xFFu;
+    return (wl & ~h) | (wh & h);
 }
 
-// Fit one subset (texels selected by mask) with one end-point pair: spec v1 steps 1-6.
-template <int IB>
-__device__ __noinline__ void fit_subset(const uint32_t (*spx)[NT], int tid, View view, uint32_t mask,
-                                        int nc, int bits, int pbmode, int ls_rounds, int pb_search,
-                                        Fit& out) {
-    // 1. integer moments of the subset
-    const int n = __popc(mask);
-    int S1[4] = {0, 0, 0, 0};
-    int S2[4][4];
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) S2[a][b] = 0;
-#pragma unroll 2
-    for (int i = 0; i < 16; i++) {
-        uint32_t p = fetch(spx, i, tid, view);
-        p = ((mask >> i) & 1u) ? p : 0u;
-        int ch[4] = {(int)(p & 255u), (int)((p >> 8) & 255u), (int)((p >> 16) & 255u), (int)(p >> 24)};
-#pragma unroll
-        for (int a = 0; a < 4; a++) {
-            S1[a] += ch[a];
-#pragma unroll
-            for (int b = a; b < 4; b++) S2[a][b] += ch[a] * ch[b];
-        }
-    }
-    float C[4][4];
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = a; b < 4; b++) C[a][b] = C[b][a] = (float)(n * S2[a][b] - S1[a] * S1[b]);
-    // 2. principal axis: 4 power iterations from the covariance column with the largest diagonal
-    float cbest = C[0][0], col[4] = {C[0][0], C[1][0], C[2][0], C[3][0]};
-#pragma unroll
-    for (int c = 1; c < 4; c++) {
-        if (C[c][c] > cbest) {
-            cbest = C[c][c];
-#pragma unroll
-            for (int a = 0; a < 4; a++) col[a] = C[a][c];
-        }
-    }
-    float v[4];
-#pragma unroll
-    for (int c = 0; c < 4; c++) v[c] = c < nc ? (cbest > 0.0f ? col[c] : 1.0f) : 0.0f;
-    for (int it = 0; it < 4; it++) {
-        float t[4], m = 0.0f;
-#pragma unroll
-        for (int a = 0; a < 4; a++) {
-            float s = 0.0f;
-#pragma unroll
-            for (int b = 0; b < 4; b++) s = s + C[a][b] * v[b];
-            t[a] = s;
-            m = fmaxf(m, fabsf(s));
-        }
-        if (m == 0.0f) break;
-        const float r = 1.0f / m;
-#pragma unroll
-        for (int a = 0; a < 4; a++) v[a] = t[a] * r;
-    }
-    float len2 = 0.0f;
-#pragma unroll
-    for (int c = 0; c < 4; c++) len2 = len2 + v[c] * v[c];
-    const float rl = 1.0f / sqrtf(len2);
-#pragma unroll
-    for (int c = 0; c < 4; c++) v[c] = v[c] * rl;
-    // 3. project, extremes along the axis
-    float mean[4];
-    const float fn = (float)n;
-#pragma unroll
-    for (int c = 0; c < 4; c++) mean[c] = (float)S1[c] / fn;
-    float tmin = 3.0e38f, tmax = -3.0e38f;
-#pragma unroll 2
-    for (int i = 0; i < 16; i++) {
-        const uint32_t p = fetch(spx, i, tid, view);
-        float t = 0.0f;
-        t = t + ((float)(p & 255u) - mean[0]) * v[0];
-        t = t + ((float)((p >> 8) & 255u) - mean[1]) * v[1];
-        t = t + ((float)((p >> 16) & 255u) - mean[2]) * v[2];
-        t = t + ((float)(p >> 24) - mean[3]) * v[3];
-        if ((mask >> i) & 1u) {
-            tmin = t < tmin ? t : tmin;
-            tmax = t > tmax ? t : tmax;
-        }
-    }
-    float lo[4], hi[4];
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        lo[c] = clampf(mean[c] + tmin * v[c], 0.0f, 255.0f);
-        hi[c] = clampf(mean[c] + tmax * v[c], 0.0f, 255.0f);
-    }
-    // 4/5/6. quantise + evaluate; then least-squares refinement rounds with the current indices
+// end-point channel x in [0,255] -> field value; `scale` = (2^(bits+1) - 1) / 255 with a p-bit
+// (LSB forced to p), (2^bits - 1) / 255 without
+__device__ __forceinline__ int quant_pbit(float x, float scale, int maxq, int p) {
+    const float y = x * scale;
+    const int q = (int)floorf((y - (float)p) * 0.5f + 0.5f);
+    return min(max(q, 0), maxq);
+}
+__device__ __forceinline__ int quant_plain(float x, float scale, int maxq) {
+    const int q = (int)floorf(x * scale + 0.5f);
+    return min(max(q, 0), maxq);
+}
+
+// One fit after `prepare`: quantise (p-bit by nearest end point, or every combination when
+// pb_search), exhaustive indices, then `ls_rounds` least-squares refinements (spec v1 steps 4-6).
+// Only `evaluate` and the weight lookup depend on the index width, so they are the only code that
+// exists per width.
+__device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, uint32_t pcmap,
+                                       uint32_t mask, int ib, int nc, int bits, int pbmode,
+                                       int ls_rounds, int pb_search, Prep& P, Fit& out) {
     out.err = 0xFFFFFFFFu;
     out.q0 = out.q1 = out.pb = 0;
     out.idx = 0;
+    const int maxq = (1 << bits) - 1;
+    const float scale = pbmode == PB_NONE ? (float)maxq / 255.0f : (float)((2 << bits) - 1) / 255.0f;
+    const uint32_t chmask = nc == 4 ? 0xFFFFFFFFu : (nc == 3 ? 0x00FFFFFFu : 0x000000FFu);
+#pragma unroll 1
     for (int round = 0; round <= ls_rounds; round++) {
         if (round > 0) {
-            int A = 0, B = 0, Cc = 0, X[4] = {0, 0, 0, 0}, Y[4] = {0, 0, 0, 0};
-#pragma unroll 2
-            for (int i = 0; i < 16; i++) {
-                const uint32_t p = fetch(spx, i, tid, view);
-                const bool in = (mask >> i) & 1u;
-                const int w = in ? weight_of<IB>((int)((out.idx >> (4 * i)) & 15u)) : 0;
-                const int u = in ? 64 - w : 0;
-                A += u * u;
-                B += u * w;
-                Cc += w * w;
-                const int ch[4] = {(int)(p & 255u), (int)((p >> 8) & 255u),
-                                   (int)((p >> 16) & 255u), (int)(p >> 24)};
+            // least squares with the current indices.  Sums over the subset, u = 64 - w:
+            //   sum u^2 = 4096 n - 128 sum w + sum w^2,  sum u w = 64 sum w - sum w^2,
+            //   X = sum u p = 64 S1 - Y,  Y = sum w p        (all exact integers)
+            int sw = 0, sww = 0, Y[4] = {0, 0, 0, 0};
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    X[c] += u * ch[c];
-                    Y[c] += w * ch[c];
-                }
+            for (int k = 0; k < 4; k++) {
+                const uint32_t nib = (uint32_t)(out.idx >> (16 * k)) & 0xFFFFu;
+                const uint32_t wq = ib == 2 ? weight_bytes<2>(nib) : (ib == 3 ? weight_bytes<3>(nib) : weight_bytes<4>(nib));
+                sw = dp4a_uu(wq, 0x01010101u, sw);
+                sww = dp4a_uu(wq, wq, sww);
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    if (c < nc) Y[c] = dp4a_uu(wq, S.pl[4 * ((pcmap >> (4 * c)) & 15u) + k][tid], Y[c]);
             }
-            const float fA = (float)A, fB = (float)B, fC = (float)Cc;
+            const float fA = (float)(4096 * P.n - 128 * sw + sww), fB = (float)(64 * sw - sww), fC = (float)sww;
             const float det = fA * fC - fB * fB;
             if (det == 0.0f) break;
-            const float k = 64.0f / det;
+            const float kk = 64.0f / det;
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                const float fx = (float)X[c], fy = (float)Y[c];
-                lo[c] = clampf((fC * fx - fB * fy) * k, 0.0f, 255.0f);
-                hi[c] = clampf((fA * fy - fB * fx) * k, 0.0f, 255.0f);
+                const float fx = (float)(64 * P.S1[c] - Y[c]), fy = (float)Y[c];
+                P.lo[c] = clampf((fC * fx - fB * fy) * kk, 0.0f, 255.0f);
+                P.hi[c] = clampf((fA * fy - fB * fx) * kk, 0.0f, 255.0f);
             }
         }
         const uint32_t before = out.err;
-        quantise_and_try<IB>(spx, tid, view, mask, nc, bits, pbmode, pb_search, lo, hi, out);
+        // ---- p-bits ----
+        int ncombo = 1;
+        uint32_t combo0 = 0;  // bit e = p-bit of end point e for combination 0
+        if (pbmode != PB_NONE) {
+            if (pb_search) {
+                ncombo = pbmode == PB_PER_EP ? 4 : 2;
+            } else {
+                // squared distance of the float end point to its quantised value, for p = 0 and p = 1:
+                // per end point (sums over c), and over both end points in (e, c) order for a shared p-bit
+                float e0s[2] = {0.0f, 0.0f}, e1s[2] = {0.0f, 0.0f}, s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        if (c < nc) {
+                            const float x = e ? P.hi[c] : P.lo[c];
+                            int q = quant_pbit(x, scale, maxq, 0);
+                            float d = (float)expand_bits(q << 1, bits + 1) - x;
+                            const float d0 = d * d;
+                            q = quant_pbit(x, scale, maxq, 1);
+                            d = (float)expand_bits((q << 1) | 1, bits + 1) - x;
+                            const float d1 = d * d;
+                            e0s[e] = e0s[e] + d0;
+                            e1s[e] = e1s[e] + d1;
+                            s0 = s0 + d0;
+                            s1 = s1 + d1;
+                        }
+                    }
+                }
+                if (pbmode == PB_PER_EP)
+                    combo0 = (e1s[0] < e0s[0] ? 1u : 0u) | (e1s[1] < e0s[1] ? 2u : 0u);
+                else
+                    combo0 = s1 < s0 ? 3u : 0u;
+            }
+        }
+#pragma unroll 1
+        for (int k = 0; k < ncombo; k++) {
+            uint32_t pb = combo0;
+            if (ncombo == 4) pb = (uint32_t)k;  // (k & 1, k >> 1)
+            if (ncombo == 2) pb = k ? 3u : 0u;
+            uint32_t q0 = 0, q1 = 0, e0 = 0, e1 = 0;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                int qa, qb, ea, eb;
+                if (pbmode == PB_NONE) {
+                    qa = quant_plain(P.lo[c], scale, maxq);
+                    qb = quant_plain(P.hi[c], scale, maxq);
+                    ea = expand_bits(qa, bits);
+                    eb = expand_bits(qb, bits);
+                } else {
+                    const int pa = pb & 1, pbb = (pb >> 1) & 1;
+                    qa = quant_pbit(P.lo[c], scale, maxq, pa);
+                    qb = quant_pbit(P.hi[c], scale, maxq, pbb);
+                    ea = expand_bits((qa << 1) | pa, bits + 1);
+                    eb = expand_bits((qb << 1) | pbb, bits + 1);
+                }
+                q0 |= (uint32_t)qa << (8 * c);
+                q1 |= (uint32_t)qb << (8 * c);
+                e0 |= (uint32_t)ea << (8 * c);
+                e1 |= (uint32_t)eb << (8 * c);
+            }
+            q0 &= chmask;
+            q1 &= chmask;
+            e0 &= chmask;
+            e1 &= chmask;
+            uint64_t idx;
+            uint32_t err;
+            if (ib == 2)
+                err = evaluate<2>(S, tid, sel, mask, e0, e1, idx);
+            else if (ib == 3)
+                err = evaluate<3>(S, tid, sel, mask, e0, e1, idx);
+            else
+                err = evaluate<4>(S, tid, sel, mask, e0, e1, idx);
+            if (err < out.err) {
+                out.err = err;
+                out.q0 = q0;
+                out.q1 = q1;
+                out.pb = pb;
+                out.idx = idx;
+            }
+        }
         if (round > 0 && out.err >= before) break;
     }
 }
@@ -457,21 +501,6 @@ __device__ __forceinline__ float kfac(int ib) {
     return 1.0f - 1.0f / (l * l);
 }
 
-// byte-planar copy of the block: plane[c][k] holds channel c of texels 4k..4k+3
-__device__ __forceinline__ void make_planes(const uint32_t (*spx)[NT], int tid, uint32_t pl[4][4]) {
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t p0 = spx[4 * k][tid], p1 = spx[4 * k + 1][tid], p2 = spx[4 * k + 2][tid],
-                       p3 = spx[4 * k + 3][tid];
-        const uint32_t t0 = __byte_perm(p0, p1, 0x5140), t1 = __byte_perm(p2, p3, 0x5140);
-        const uint32_t t2 = __byte_perm(p0, p1, 0x7362), t3 = __byte_perm(p2, p3, 0x7362);
-        pl[0][k] = __byte_perm(t0, t1, 0x5410);
-        pl[1][k] = __byte_perm(t0, t1, 0x7632);
-        pl[2][k] = __byte_perm(t2, t3, 0x5410);
-        pl[3][k] = __byte_perm(t2, t3, 0x7632);
-    }
-}
-
 // integer moments of the texels selected by the byte masks mk[4]
 template <int NC>
 __device__ __forceinline__ void masked_moments(const uint32_t pl[4][4], const uint32_t mk[4],
@@ -496,18 +525,24 @@ __device__ __forceinline__ void masked_moments(const uint32_t pl[4][4], const ui
     }
 }
 
-// Rank the partitions of a 2- or 3-subset table for two index widths at once.
+// Rank the partitions of a 2- or 3-subset table for two index widths at once; the best TOPK of
+// each list go to S.parts rows rowA.. and rowB.. (rowB < 0: second list not wanted).
 template <int NC, int NS>
-__device__ __noinline__ void estimate_partitions(const uint32_t (*spx)[NT], int tid, int nparts,
-                                                 int ibA, int ibB, TopList& listA, TopList& listB) {
+__device__ __forceinline__ void estimate_partitions(Shared& S, int tid, int nparts, int ibA, int ibB,
+                                                    int rowA, int rowB) {
     uint32_t pl[4][4];
-    make_planes(spx, tid, pl);
+#pragma unroll
+    for (int c = 0; c < 4; c++)
+#pragma unroll
+        for (int k = 0; k < 4; k++) pl[c][k] = S.pl[4 * c + k][tid];
     const uint32_t ones[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
     int T1[4], T2[4][4];
     masked_moments<NC>(pl, ones, T1, T2);
+    TopList listA, listB;
     top_init(listA);
     top_init(listB);
     const float kA = kfac(ibA), kB = kfac(ibB);
+#pragma unroll 1
     for (int p = 0; p < nparts; p++) {
         int S1[3][4], S2[3][4][4], n[3];
         uint32_t mk[4];
@@ -547,98 +582,27 @@ __device__ __noinline__ void estimate_partitions(const uint32_t (*spx)[NT], int 
         top_insert(listA, A - kA * B, p);
         top_insert(listB, A - kB * B, p);
     }
+#pragma unroll
+    for (int k = 0; k < TOPK; k++) {
+        S.parts[rowA + k][tid] = (uint8_t)(listA.key[k] & 63u);
+        if (rowB >= 0) S.parts[rowB + k][tid] = (uint8_t)(listB.key[k] & 63u);
+    }
 }
 
-// ---- candidates ------------------------------------------------------------------------------
+// ---- bit packing -----------------------------------------------------------------------------
 
 __device__ __forceinline__ void subset_masks(int ns, int partition, uint32_t masks[3]) {
     masks[0] = 0xFFFFu;
     masks[1] = masks[2] = 0u;
     if (ns == 2) {
-        masks[1] = g_P2M[partition];
+        masks[1] = c_PART2_MASK[partition];
         masks[0] = 0xFFFFu & ~masks[1];
     } else if (ns == 3) {
-        masks[1] = g_P3M1[partition];
-        masks[2] = g_P3M2[partition];
+        masks[1] = c_P3M1[partition];
+        masks[2] = c_P3M2[partition];
         masks[0] = 0xFFFFu & ~(masks[1] | masks[2]);
     }
 }
-
-template <int IB>
-__device__ __noinline__ void try_partitioned(const uint32_t (*spx)[NT], int tid, int mode, int ns,
-                                             int nc, int bits, int pbmode, int partition,
-                                             int ls_rounds, int pb_search, Solution& best) {
-    uint32_t masks[3];
-    subset_masks(ns, partition, masks);
-    const View view = {0x3210u, nc == 4 ? 0xFFFFFFFFu : 0x00FFFFFFu};
-    Solution s;
-    s.mode = mode;
-    s.partition = partition;
-    s.rotation = 0;
-    s.idxsel = 0;
-    s.err = 0;
-    s.pb = 0;
-    s.idx = 0;
-    s.idx2 = 0;
-#pragma unroll
-    for (int k = 0; k < 3; k++) s.q[k][0] = s.q[k][1] = 0;
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        if (k < ns) {
-            Fit f;
-            fit_subset<IB>(spx, tid, view, masks[k], nc, bits, pbmode, ls_rounds, pb_search, f);
-            s.q[k][0] = f.q0;
-            s.q[k][1] = f.q1;
-            s.pb |= f.pb << (2 * k);
-            s.idx |= f.idx;
-            s.err += f.err;
-        }
-    }
-    if (s.err < best.err) best = s;
-}
-
-__device__ __noinline__ void try_mode45(const uint32_t (*spx)[NT], int tid, int mode, int rotation,
-                                        int idxsel, int ls_rounds, int pb_search, Solution& best) {
-    // rotation r swaps alpha with channel r-1.  __byte_perm selectors (nibble i picks result
-    // byte i; 4 = zero): colour view = rotated (c0,c1,c2,0), scalar view = rotated alpha in byte 0
-    uint32_t colsel, scasel;
-    switch (rotation) {
-        default: colsel = 0x4210u; scasel = 0x4443u; break;  // (R,G,B) | A
-        case 1:  colsel = 0x4213u; scasel = 0x4440u; break;  // (A,G,B) | R
-        case 2:  colsel = 0x4230u; scasel = 0x4441u; break;  // (R,A,B) | G
-        case 3:  colsel = 0x4310u; scasel = 0x4442u; break;  // (R,G,A) | B
-    }
-    const View cview = {colsel, 0xFFFFFFFFu}, aview = {scasel, 0xFFFFFFFFu};
-    const int cb = mode == 4 ? 5 : 7, ab = mode == 4 ? 6 : 8;
-    Fit fc, fa;
-    if (mode == 5 || !idxsel) {  // colour 2-bit, scalar 2-bit (mode 5) or 3-bit (mode 4)
-        fit_subset<2>(spx, tid, cview, 0xFFFFu, 3, cb, PB_NONE, ls_rounds, pb_search, fc);
-        if (mode == 5)
-            fit_subset<2>(spx, tid, aview, 0xFFFFu, 1, ab, PB_NONE, ls_rounds, pb_search, fa);
-        else
-            fit_subset<3>(spx, tid, aview, 0xFFFFu, 1, ab, PB_NONE, ls_rounds, pb_search, fa);
-    } else {  // mode 4, index selector 1: colour 3-bit, scalar 2-bit
-        fit_subset<3>(spx, tid, cview, 0xFFFFu, 3, cb, PB_NONE, ls_rounds, pb_search, fc);
-        fit_subset<2>(spx, tid, aview, 0xFFFFu, 1, ab, PB_NONE, ls_rounds, pb_search, fa);
-    }
-    const uint32_t err = fc.err + fa.err;
-    if (err < best.err) {
-        best.mode = mode;
-        best.partition = 0;
-        best.rotation = rotation;
-        best.idxsel = idxsel;
-        best.err = err;
-        best.pb = 0;
-        best.q[0][0] = (fc.q0 & 0x00FFFFFFu) | (fa.q0 << 24);
-        best.q[0][1] = (fc.q1 & 0x00FFFFFFu) | (fa.q1 << 24);
-        best.q[1][0] = best.q[1][1] = best.q[2][0] = best.q[2][1] = 0;
-        // the primary index set is the 2-bit one: colour when idxsel == 0, the scalar otherwise
-        best.idx = idxsel ? fa.idx : fc.idx;
-        best.idx2 = idxsel ? fc.idx : fa.idx;
-    }
-}
-
-// ---- bit packing -----------------------------------------------------------------------------
 
 struct Bits128 {
     uint64_t lo, hi;
@@ -671,8 +635,19 @@ __device__ __forceinline__ void swap_endpoint_bytes(uint32_t& a, uint32_t& b, ui
     b = nb;
 }
 
-__device__ __noinline__ void pack_solution(Solution& s, uint4& out) {
-    const int mode = s.mode;
+// the thread's best solution (S.best column) -> 128-bit block
+__device__ __forceinline__ uint4 pack_solution(const Shared& S, int tid) {
+    uint32_t q[3][2];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        q[k][0] = S.best[2 * k][tid];
+        q[k][1] = S.best[2 * k + 1][tid];
+    }
+    uint32_t pb = S.best[6][tid];
+    uint64_t idx = (uint64_t)S.best[7][tid] | ((uint64_t)S.best[8][tid] << 32);
+    uint64_t idx2 = (uint64_t)S.best[9][tid] | ((uint64_t)S.best[10][tid] << 32);
+    const uint32_t meta = S.best[11][tid];
+    const int mode = meta & 7, partition = (meta >> 3) & 63, rotation = (meta >> 9) & 3, idxsel = (meta >> 11) & 1;
     const int ns = (mode == 0 || mode == 2) ? 3 : ((mode == 1 || mode == 3 || mode == 7) ? 2 : 1);
     const int part_bits = mode == 0 ? 4 : (ns > 1 ? 6 : 0);
     const int rb = (mode == 4 || mode == 5) ? 2 : 0, isb = mode == 4 ? 1 : 0;
@@ -682,79 +657,75 @@ __device__ __noinline__ void pack_solution(Solution& s, uint4& out) {
     const bool epb = (mode == 0 || mode == 3 || mode == 6 || mode == 7), spb = mode == 1;
     int anchor[3] = {0, -1, -1};
     uint32_t masks[3];
-    subset_masks(ns, s.partition, masks);
-    if (ns == 2) anchor[1] = g_ANCHOR2[s.partition];
+    subset_masks(ns, partition, masks);
+    if (ns == 2) anchor[1] = c_ANCHOR2[partition];
     if (ns == 3) {
-        anchor[1] = g_ANCHOR3A[s.partition];
-        anchor[2] = g_ANCHOR3B[s.partition];
+        anchor[1] = c_ANCHOR3A[partition];
+        anchor[2] = c_ANCHOR3B[partition];
     }
     // anchor rule: the anchor texel's index must have a clear MSB; swap the end points if not
     const uint64_t maxi = (1u << ib) - 1u;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-        if (k < ns && ((s.idx >> (4 * anchor[k] + ib - 1)) & 1ull)) {
+        if (k < ns && ((idx >> (4 * anchor[k] + ib - 1)) & 1ull)) {
             const uint64_t lanes = lanes_of(masks[k]);
-            s.idx = (s.idx & ~(lanes * 15ull)) | (lanes * maxi - (s.idx & (lanes * 15ull)));
+            idx = (idx & ~(lanes * 15ull)) | (lanes * maxi - (idx & (lanes * 15ull)));
             if (ib2 == 0) {  // one index set drives every channel (and the p-bits)
-                swap_endpoint_bytes(s.q[k][0], s.q[k][1], 0xFFFFFFFFu);
-                const uint32_t p0 = (s.pb >> (2 * k)) & 1u, p1 = (s.pb >> (2 * k + 1)) & 1u;
-                s.pb = (s.pb & ~(3u << (2 * k))) | (p1 << (2 * k)) | (p0 << (2 * k + 1));
+                swap_endpoint_bytes(q[k][0], q[k][1], 0xFFFFFFFFu);
+                const uint32_t p0 = (pb >> (2 * k)) & 1u, p1 = (pb >> (2 * k + 1)) & 1u;
+                pb = (pb & ~(3u << (2 * k))) | (p1 << (2 * k)) | (p0 << (2 * k + 1));
             } else {  // modes 4/5: the primary set is colour (idxsel 0) or alpha (idxsel 1)
-                swap_endpoint_bytes(s.q[k][0], s.q[k][1], s.idxsel ? 0xFF000000u : 0x00FFFFFFu);
+                swap_endpoint_bytes(q[k][0], q[k][1], idxsel ? 0xFF000000u : 0x00FFFFFFu);
             }
         }
     }
-    if (ib2 && ((s.idx2 >> (ib2 - 1)) & 1ull)) {
+    if (ib2 && ((idx2 >> (ib2 - 1)) & 1ull)) {
         const uint64_t maxi2 = (1u << ib2) - 1u;
-        s.idx2 = 0x1111111111111111ull * maxi2 - s.idx2;
-        swap_endpoint_bytes(s.q[0][0], s.q[0][1], s.idxsel ? 0x00FFFFFFu : 0xFF000000u);
+        idx2 = 0x1111111111111111ull * maxi2 - idx2;
+        swap_endpoint_bytes(q[0][0], q[0][1], idxsel ? 0x00FFFFFFu : 0xFF000000u);
     }
     Bits128 w = {0ull, 0ull, 0};
     put(w, 1u << mode, mode + 1);
-    put(w, (uint32_t)s.partition, part_bits);
-    put(w, (uint32_t)s.rotation, rb);
-    put(w, (uint32_t)s.idxsel, isb);
+    put(w, (uint32_t)partition, part_bits);
+    put(w, (uint32_t)rotation, rb);
+    put(w, (uint32_t)idxsel, isb);
 #pragma unroll
     for (int c = 0; c < 3; c++)
 #pragma unroll
         for (int k = 0; k < 3; k++)
             if (k < ns) {
-                put(w, (s.q[k][0] >> (8 * c)) & 255u, cb);
-                put(w, (s.q[k][1] >> (8 * c)) & 255u, cb);
+                put(w, (q[k][0] >> (8 * c)) & 255u, cb);
+                put(w, (q[k][1] >> (8 * c)) & 255u, cb);
             }
     if (ab) {
 #pragma unroll
         for (int k = 0; k < 3; k++)
             if (k < ns) {
-                put(w, s.q[k][0] >> 24, ab);
-                put(w, s.q[k][1] >> 24, ab);
+                put(w, q[k][0] >> 24, ab);
+                put(w, q[k][1] >> 24, ab);
             }
     }
-    if (epb) put(w, s.pb & ((1u << (2 * ns)) - 1u), 2 * ns);
+    if (epb) put(w, pb & ((1u << (2 * ns)) - 1u), 2 * ns);
     if (spb) {
-        put(w, s.pb & 1u, 1);
-        put(w, (s.pb >> 2) & 1u, 1);
+        put(w, pb & 1u, 1);
+        put(w, (pb >> 2) & 1u, 1);
     }
+#pragma unroll 1
     for (int i = 0; i < 16; i++) {
         const int is_anchor = (i == anchor[0]) || (i == anchor[1]) || (i == anchor[2]);
-        put(w, (uint32_t)((s.idx >> (4 * i)) & 15ull), ib - is_anchor);
+        put(w, (uint32_t)((idx >> (4 * i)) & 15ull), ib - is_anchor);
     }
-    if (ib2)
-        for (int i = 0; i < 16; i++) put(w, (uint32_t)((s.idx2 >> (4 * i)) & 15ull), ib2 - (i == 0));
-    out = make_uint4((uint32_t)w.lo, (uint32_t)(w.lo >> 32), (uint32_t)w.hi, (uint32_t)(w.hi >> 32));
-}
-
-__device__ __forceinline__ int top_pop(TopList& t) {
-    const int part = (int)(t.key[0] & 63u);
-#pragma unroll
-    for (int k = 0; k + 1 < TOPK; k++) t.key[k] = t.key[k + 1];
-    return part;
+    if (ib2) {
+#pragma unroll 1
+        for (int i = 0; i < 16; i++) put(w, (uint32_t)((idx2 >> (4 * i)) & 15ull), ib2 - (i == 0));
+    }
+    return make_uint4((uint32_t)w.lo, (uint32_t)(w.lo >> 32), (uint32_t)w.hi, (uint32_t)(w.hi >> 32));
 }
 
 // ---- kernel ----------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(NT) bc7_encode_kernel(const __grid_constant__ Params P) {
-    __shared__ uint32_t spx[16][NT];
+    __shared__ Shared S;
     const int tid = threadIdx.x;
     const uint64_t b = (uint64_t)blockIdx.x * NT + tid;
     const bool live = b < P.num_blocks;
@@ -773,41 +744,39 @@ __global__ void __launch_bounds__(NT) bc7_encode_kernel(const __grid_constant__ 
         for (int y = 0; y < 4; y++) {
             const uint4 r = __ldg(reinterpret_cast<const uint4*>(
                 base + 4ull * ((uint64_t)(4 * by + y) * lv.w + 4 * bx)));
-            spx[4 * y + 0][tid] = r.x;
-            spx[4 * y + 1][tid] = r.y;
-            spx[4 * y + 2][tid] = r.z;
-            spx[4 * y + 3][tid] = r.w;
+            S.px[4 * y + 0][tid] = r.x;
+            S.px[4 * y + 1][tid] = r.y;
+            S.px[4 * y + 2][tid] = r.z;
+            S.px[4 * y + 3][tid] = r.w;
         }
     } else {
         for (int y = 0; y < 4; y++)
             for (int x = 0; x < 4; x++) {
                 const uint32_t sx = min(4 * bx + x, lv.w - 1), sy = min(4 * by + y, lv.h - 1);
-                spx[4 * y + x][tid] =
+                S.px[4 * y + x][tid] =
                     __ldg(reinterpret_cast<const uint32_t*>(base) + (uint64_t)sy * lv.w + sx);
             }
     }
-    // every thread only ever reads its own column of spx: no barrier needed
-    const uint32_t p0 = spx[0][tid];
+    // every thread only ever touches its own column of S: no barrier needed anywhere
+    const uint32_t p0 = S.px[0][tid];
     bool solid = true, has_alpha = false;
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t p = spx[i][tid];
-        solid = solid && (p == p0);
-        has_alpha = has_alpha || ((p >> 24) != 255u);
+    for (int k = 0; k < 4; k++) {
+        const uint32_t a = S.px[4 * k][tid], bq = S.px[4 * k + 1][tid], c = S.px[4 * k + 2][tid],
+                       d = S.px[4 * k + 3][tid];
+        solid = solid && a == p0 && bq == p0 && c == p0 && d == p0;
+        has_alpha = has_alpha || ((a & bq & c & d) >> 24) != 255u;
+        // byte planes: channel c of texels 4k..4k+3
+        const uint32_t t0 = __byte_perm(a, bq, 0x5140), t1 = __byte_perm(c, d, 0x5140);
+        const uint32_t t2 = __byte_perm(a, bq, 0x7362), t3 = __byte_perm(c, d, 0x7362);
+        S.pl[0 + k][tid] = __byte_perm(t0, t1, 0x5410);
+        S.pl[4 + k][tid] = __byte_perm(t0, t1, 0x7632);
+        S.pl[8 + k][tid] = __byte_perm(t2, t3, 0x5410);
+        S.pl[12 + k][tid] = __byte_perm(t2, t3, 0x7632);
     }
-    const int n1 = P.tier.n1, n3 = P.tier.n3, n0 = P.tier.n0, n2 = P.tier.n2, n7 = P.tier.n7;
-    const int ls = P.tier.ls_rounds, pbs = P.tier.pb_search;
-    Solution best;
-    best.err = 0xFFFFFFFFu;
-    best.mode = 6;
-    best.partition = best.rotation = best.idxsel = 0;
-    best.pb = 0;
-    best.idx = best.idx2 = 0;
-#pragma unroll
-    for (int k = 0; k < 3; k++) best.q[k][0] = best.q[k][1] = 0;
+    uint32_t best_err = 0xFFFFFFFFu;
     if (solid) {
         // exact (or nearest) single colour: mode 5, rotation 0, colour index 1, alpha index 0
-        best.mode = 5;
         uint32_t q0 = 0, q1 = 0;
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -815,58 +784,207 @@ __global__ void __launch_bounds__(NT) bc7_encode_kernel(const __grid_constant__ 
             q0 |= (uint32_t)c_SOLID5[v][0] << (8 * c);
             q1 |= (uint32_t)c_SOLID5[v][1] << (8 * c);
         }
-        best.q[0][0] = q0 | (p0 & 0xFF000000u);
-        best.q[0][1] = q1 | (p0 & 0xFF000000u);
-        best.idx = 0x1111111111111111ull;
-    } else {
-        // mode 6: one subset, RGBA 7.7.7.7 + p-bit per end point, 4-bit indices
-        try_partitioned<4>(spx, tid, 6, 1, 4, 7, PB_PER_EP, 0, ls, pbs, best);
-        if (!has_alpha) {
-            if (n1 | n3) {
-                TopList l1, l3;
-                estimate_partitions<3, 2>(spx, tid, 64, 3, 2, l1, l3);
-                for (int i = 0; i < n1; i++)
-                    try_partitioned<3>(spx, tid, 1, 2, 3, 6, PB_SHARED, top_pop(l1), ls, pbs, best);
-                for (int i = 0; i < n3; i++)
-                    try_partitioned<2>(spx, tid, 3, 2, 3, 7, PB_PER_EP, top_pop(l3), ls, pbs, best);
-            }
-            if (n0 | n2) {
-                TopList l0, l2, dummy;
-                estimate_partitions<3, 3>(spx, tid, 16, 3, 2, l0, dummy);
-                estimate_partitions<3, 3>(spx, tid, 64, 2, 2, l2, dummy);
-                for (int i = 0; i < n0; i++)
-                    try_partitioned<3>(spx, tid, 0, 3, 3, 4, PB_PER_EP, top_pop(l0), ls, pbs, best);
-                for (int i = 0; i < n2; i++)
-                    try_partitioned<2>(spx, tid, 2, 3, 3, 5, PB_NONE, top_pop(l2), ls, pbs, best);
-            }
-        } else if (n7) {
-            TopList l7, dummy;
-            estimate_partitions<4, 2>(spx, tid, 64, 2, 2, l7, dummy);
-            for (int i = 0; i < n7; i++)
-                try_partitioned<2>(spx, tid, 7, 2, 4, 5, PB_PER_EP, top_pop(l7), ls, pbs, best);
+        S.best[0][tid] = q0 | (p0 & 0xFF000000u);
+        S.best[1][tid] = q1 | (p0 & 0xFF000000u);
+#pragma unroll
+        for (int f = 2; f < 11; f++) S.best[f][tid] = 0u;
+        S.best[7][tid] = 0x11111111u;
+        S.best[8][tid] = 0x11111111u;
+        S.best[11][tid] = 5u;
+    }
+    const bool search = live && !solid;
+    const int tier = P.tier;
+    const int ls = P.ls_rounds, pbs = P.pb_search;
+    // candidate under construction
+    uint32_t cq[3][2] = {{0, 0}, {0, 0}, {0, 0}}, cpb = 0, cerr = 0;
+    uint64_t cidx = 0, cidx2 = 0;
+    const int njobs = c_NJOBS[tier];
+#pragma unroll 1
+    for (int j = 0; j < njobs; j++) {
+        const uint2 jw = c_JOBS[tier][j];
+        const int type = jw.x & 3, areq = (jw.y >> 4) & 3;
+        const bool on = search && (areq == AREQ_ANY || (areq == AREQ_ALPHA) == has_alpha);
+        if (!on) continue;
+        if (type == JOB_EST) {
+            const int kind = (jw.y >> 11) & 3;
+            if (kind == 0)
+                estimate_partitions<3, 2>(S, tid, 64, 3, 2, 0 * TOPK, 1 * TOPK);
+            else if (kind == 3)
+                estimate_partitions<4, 2>(S, tid, 64, 2, 2, 4 * TOPK, -1);
+            else
+                estimate_partitions<3, 3>(S, tid, kind == 1 ? 16 : 64, kind == 1 ? 3 : 2, 2,
+                                          kind == 1 ? 2 * TOPK : 3 * TOPK, -1);
+            continue;
         }
-        for (int r = 0; r < P.tier.rot5; r++) try_mode45(spx, tid, 5, r, 0, ls, pbs, best);
-        for (int r = 0; r < P.tier.rot4; r++) {
-            try_mode45(spx, tid, 4, r, 0, ls, pbs, best);
-            try_mode45(spx, tid, 4, r, 1, ls, pbs, best);
+        Prep pr;
+        if (type == JOB_PREP_P3) {
+            prepare<3>(S, tid, c_VIEW_SEL[1], c_VIEW_PC[1], 0xFFFFu, pr);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                S.p3[c][tid] = __float_as_uint(pr.lo[c]);
+                S.p3[4 + c][tid] = __float_as_uint(pr.hi[c]);
+                S.p3[8 + c][tid] = (uint32_t)pr.S1[c];
+            }
+            continue;
+        }
+        // ---- a fit ----
+        const int mode = (jw.x >> 2) & 7, ns = (jw.x >> 5) & 3, k = (jw.x >> 7) & 3, prow = (jw.x >> 9) & 63;
+        const int view = (jw.x >> 15) & 15, nc = (jw.x >> 19) & 7, ib = (jw.x >> 22) & 7;
+        const int bits = (jw.x >> 25) & 15, pbmode = (jw.x >> 29) & 3;
+        const int prep = jw.y & 3, first = (jw.y >> 2) & 1, last = (jw.y >> 3) & 1, dest = (jw.y >> 6) & 3;
+        const int idxsel = (jw.y >> 8) & 1, rot = (jw.y >> 9) & 3;
+        const uint32_t sel = c_VIEW_SEL[view], pcmap = c_VIEW_PC[view];
+        const int partition = prow < 63 ? (int)S.parts[prow][tid] : 0;
+        uint32_t mask = 0xFFFFu;
+        if (ns == 2) {
+            const uint32_t m1 = c_PART2_MASK[partition];
+            mask = k ? m1 : (0xFFFFu & ~m1);
+        } else if (ns == 3) {
+            const uint32_t m1 = c_P3M1[partition], m2 = c_P3M2[partition];
+            mask = k == 0 ? (0xFFFFu & ~(m1 | m2)) : (k == 1 ? m1 : m2);
+        }
+        if (prep == PREP_COMPUTE || (prep == PREP_MODE6 && has_alpha)) {
+            if (nc == 4)
+                prepare<4>(S, tid, sel, pcmap, mask, pr);
+            else if (nc == 3)
+                prepare<3>(S, tid, sel, pcmap, mask, pr);
+            else
+                prepare<1>(S, tid, sel, pcmap, mask, pr);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                pr.lo[c] = __uint_as_float(S.p3[c][tid]);
+                pr.hi[c] = __uint_as_float(S.p3[4 + c][tid]);
+                pr.S1[c] = (int)S.p3[8 + c][tid];
+            }
+            pr.n = 16;
+            if (prep == PREP_MODE6) {  // opaque block: the RGBA fit is the RGB fit with alpha = 255
+                pr.lo[3] = pr.hi[3] = 255.0f;
+                pr.S1[3] = 16 * 255;
+            }
+        }
+        Fit f;
+        refine(S, tid, sel, pcmap, mask, ib, nc, bits, pbmode, ls, pbs, pr, f);
+        // ---- accumulate into the candidate ----
+        if (first) {
+#pragma unroll
+            for (int s = 0; s < 3; s++) cq[s][0] = cq[s][1] = 0;
+            cpb = 0;
+            cerr = 0;
+            cidx = cidx2 = 0;
+        }
+        if (dest == DEST_PART) {
+            if (k == 0) {
+                cq[0][0] = f.q0;
+                cq[0][1] = f.q1;
+            } else if (k == 1) {
+                cq[1][0] = f.q0;
+                cq[1][1] = f.q1;
+            } else {
+                cq[2][0] = f.q0;
+                cq[2][1] = f.q1;
+            }
+            cpb |= f.pb << (2 * k);
+            cidx |= f.idx;
+            cerr += f.err;
+        } else if (dest == DEST_COLOUR) {
+            cq[0][0] = f.q0 & 0x00FFFFFFu;
+            cq[0][1] = f.q1 & 0x00FFFFFFu;
+            cidx = f.idx;
+            cerr = f.err;
+        } else {
+            cq[0][0] |= f.q0 << 24;
+            cq[0][1] |= f.q1 << 24;
+            cerr += f.err;
+            // the primary index set is the 2-bit one: colour when idxsel == 0, the scalar otherwise
+            if (idxsel) {
+                cidx2 = cidx;
+                cidx = f.idx;
+            } else {
+                cidx2 = f.idx;
+            }
+        }
+        if (last && cerr < best_err) {
+            best_err = cerr;
+#pragma unroll
+            for (int s = 0; s < 3; s++) {
+                S.best[2 * s][tid] = cq[s][0];
+                S.best[2 * s + 1][tid] = cq[s][1];
+            }
+            S.best[6][tid] = cpb;
+            S.best[7][tid] = (uint32_t)cidx;
+            S.best[8][tid] = (uint32_t)(cidx >> 32);
+            S.best[9][tid] = (uint32_t)cidx2;
+            S.best[10][tid] = (uint32_t)(cidx2 >> 32);
+            S.best[11][tid] = (uint32_t)mode | ((uint32_t)partition << 3) | ((uint32_t)rot << 9) | ((uint32_t)idxsel << 11);
         }
     }
-    uint4 outv;
-    pack_solution(best, outv);
-    if (live) reinterpret_cast<uint4*>(P.out)[b] = outv;
+    if (live) reinterpret_cast<uint4*>(P.out)[b] = pack_solution(S, tid);
 }
 
 }  // namespace
 
 // fast / normal / high  ~  nvtt::Quality_Fastest / Normal / Production
-Bc7Tier bc7_tier(int quality) {
-    static const Bc7Tier tiers[3] = {
-        {1, 0, 0, 0, 1, 1, 0, 1, 0},
-        {3, 2, 0, 0, 2, 4, 1, 2, 0},
-        {6, 4, 3, 3, 4, 4, 4, 3, 1},
+static const Bc7Tier kTiers[3] = {
+    {1, 0, 0, 0, 1, 1, 0, 1, 0},
+    {3, 2, 0, 0, 2, 4, 1, 2, 0},
+    {6, 4, 3, 3, 4, 4, 4, 3, 1},
+};
+Bc7Tier bc7_tier(int quality) { return kTiers[quality < 0 ? 0 : (quality > 2 ? 2 : quality)]; }
+
+namespace {
+// the search of one tier as a job list, in the order of the specification (ties keep the earlier candidate)
+int build_jobs(const Bc7Tier& t, uint2* out) {
+    int n = 0;
+    auto fit = [&](int mode, int ns, int k, int prow, int view, int nc, int ib, int bits, int pbmode, int prep,
+                   int first, int last, int areq, int dest, int idxsel, int rot) {
+        JobFields j = {JOB_FIT, mode, ns, k, prow, view, nc, ib, bits, pbmode, prep, first, last, areq, dest, idxsel, rot, 0};
+        out[n++] = pack_job(j);
     };
-    return tiers[quality < 0 ? 0 : (quality > 2 ? 2 : quality)];
+    auto est = [&](int kind, int areq) {
+        JobFields j = {JOB_EST, 0, 0, 0, 63, 0, 0, 0, 0, 0, 0, 0, 0, areq, 0, 0, 0, kind};
+        out[n++] = pack_job(j);
+    };
+    JobFields p3 = {JOB_PREP_P3, 0, 0, 0, 63, 1, 3, 0, 0, 0, 0, 0, 0, AREQ_ANY, 0, 0, 0, 0};
+    out[n++] = pack_job(p3);
+    fit(6, 1, 0, 63, 0, 4, 4, 7, PB_PER_EP, PREP_MODE6, 1, 1, AREQ_ANY, DEST_PART, 0, 0);
+    if (t.n1 | t.n3) {
+        est(0, AREQ_OPAQUE);
+        for (int i = 0; i < t.n1; i++)
+            for (int k = 0; k < 2; k++)
+                fit(1, 2, k, 0 * TOPK + i, 1, 3, 3, 6, PB_SHARED, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
+        for (int i = 0; i < t.n3; i++)
+            for (int k = 0; k < 2; k++)
+                fit(3, 2, k, 1 * TOPK + i, 1, 3, 2, 7, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
+    }
+    if (t.n0 | t.n2) {
+        if (t.n0) est(1, AREQ_OPAQUE);
+        if (t.n2) est(2, AREQ_OPAQUE);
+        for (int i = 0; i < t.n0; i++)
+            for (int k = 0; k < 3; k++)
+                fit(0, 3, k, 2 * TOPK + i, 1, 3, 3, 4, PB_PER_EP, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
+        for (int i = 0; i < t.n2; i++)
+            for (int k = 0; k < 3; k++)
+                fit(2, 3, k, 3 * TOPK + i, 1, 3, 2, 5, PB_NONE, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
+    }
+    if (t.n7) {
+        est(3, AREQ_ALPHA);
+        for (int i = 0; i < t.n7; i++)
+            for (int k = 0; k < 2; k++)
+                fit(7, 2, k, 4 * TOPK + i, 0, 4, 2, 5, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_ALPHA, DEST_PART, 0, 0);
+    }
+    for (int r = 0; r < t.rot5; r++) {
+        fit(5, 1, 0, 63, r == 0 ? 1 : 1 + r, 3, 2, 7, PB_NONE, r == 0 ? PREP_FROM_P3 : PREP_COMPUTE, 1, 0, AREQ_ANY, DEST_COLOUR, 0, r);
+        fit(5, 1, 0, 63, 5 + r, 1, 2, 8, PB_NONE, PREP_COMPUTE, 0, 1, AREQ_ANY, DEST_SCALAR, 0, r);
+    }
+    for (int r = 0; r < t.rot4; r++)
+        for (int s = 0; s < 2; s++) {
+            fit(4, 1, 0, 63, r == 0 ? 1 : 1 + r, 3, s ? 3 : 2, 5, PB_NONE, r == 0 ? PREP_FROM_P3 : PREP_COMPUTE, 1, 0, AREQ_ANY, DEST_COLOUR, s, r);
+            fit(4, 1, 0, 63, 5 + r, 1, s ? 2 : 3, 6, PB_NONE, PREP_COMPUTE, 0, 1, AREQ_ANY, DEST_SCALAR, s, r);
+        }
+    return n;
 }
+}  // namespace
 
 // Derived lookup tables, uploaded once per device.
 int bc7_upload_tables() {
@@ -906,6 +1024,12 @@ int bc7_upload_tables() {
             }
         }
     }
+    static uint2 jobs[3][MAXJOBS];
+    int njobs[3];
+    for (int t = 0; t < 3; t++) {
+        njobs[t] = build_jobs(kTiers[t], jobs[t]);
+        if (njobs[t] > MAXJOBS) return -1;
+    }
     cudaError_t e = cudaSuccess;
     auto ok = [&](cudaError_t r) {
         if (e == cudaSuccess) e = r;
@@ -913,20 +1037,23 @@ int bc7_upload_tables() {
     ok(cudaMemcpyToSymbol(c_SOLID5, solid5, sizeof solid5));
     ok(cudaMemcpyToSymbol(c_PART2_BYTES, p2b, sizeof p2b));
     ok(cudaMemcpyToSymbol(c_PART3_BYTES, p3b, sizeof p3b));
-    ok(cudaMemcpyToSymbol(g_P3M1, p3m1, sizeof p3m1));
-    ok(cudaMemcpyToSymbol(g_P3M2, p3m2, sizeof p3m2));
-    ok(cudaMemcpyToSymbol(g_P2M, h_PART2_MASK, sizeof h_PART2_MASK));
-    ok(cudaMemcpyToSymbol(g_ANCHOR2, h_ANCHOR2, sizeof h_ANCHOR2));
-    ok(cudaMemcpyToSymbol(g_ANCHOR3A, h_ANCHOR3A, sizeof h_ANCHOR3A));
-    ok(cudaMemcpyToSymbol(g_ANCHOR3B, h_ANCHOR3B, sizeof h_ANCHOR3B));
+    ok(cudaMemcpyToSymbol(c_P3M1, p3m1, sizeof p3m1));
+    ok(cudaMemcpyToSymbol(c_P3M2, p3m2, sizeof p3m2));
+    ok(cudaMemcpyToSymbol(c_ANCHOR2, h_ANCHOR2, sizeof h_ANCHOR2));
+    ok(cudaMemcpyToSymbol(c_ANCHOR3A, h_ANCHOR3A, sizeof h_ANCHOR3A));
+    ok(cudaMemcpyToSymbol(c_ANCHOR3B, h_ANCHOR3B, sizeof h_ANCHOR3B));
+    ok(cudaMemcpyToSymbol(c_JOBS, jobs, sizeof jobs));
+    ok(cudaMemcpyToSymbol(c_NJOBS, njobs, sizeof njobs));
     return e == cudaSuccess ? 0 : -1;
 }
 
-int launch_bc7(const Chain& c, int first_level, int num_levels, const Bc7Tier& t,
-               const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
+int launch_bc7(const Chain& c, int first_level, int num_levels, int quality, const uint8_t* d_level0,
+               const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
     Params P;
     P.chain = c;
-    P.tier = t;
+    P.tier = quality < 0 ? 0 : (quality > 2 ? 2 : quality);
+    P.ls_rounds = kTiers[P.tier].ls_rounds;
+    P.pb_search = kTiers[P.tier].pb_search;
     P.level0 = d_level0;
     P.chainbuf = d_chain;
     P.first_level = first_level;

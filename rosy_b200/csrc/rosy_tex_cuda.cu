@@ -257,7 +257,7 @@ int encode_on_stream(const Chain& c, const Resolved& r, const uint8_t* d_rgba, u
         const uint8_t* level0 = r.normal_map ? nullptr : d_rgba;
         int n;
         if (r.format == ROSY_TEX_FORMAT_BC7)
-            n = launch_bc7(c, 0, c.levels, bc7_tier(r.quality), level0, d_chain, d_blocks, stream);
+            n = launch_bc7(c, 0, c.levels, r.quality, level0, d_chain, d_blocks, stream);
         else
             n = launch_bc45(c, 0, c.levels, r.format == ROSY_TEX_FORMAT_BC5, level0, d_chain, d_blocks, stream);
         if (n < 0) return cuda_fail(cudaGetLastError(), "encoder kernel");

@@ -46,7 +46,7 @@ size_t mips_scratch_bytes(const Chain& c);
 int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
                 const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
 // bc7_encode.cu
-int launch_bc7(const Chain& c, int first_level, int num_levels, const Bc7Tier& t,
+int launch_bc7(const Chain& c, int first_level, int num_levels, int quality,
                const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
 int bc7_upload_tables();   // per device, once
 int mips_upload_tables();  // per device, once
