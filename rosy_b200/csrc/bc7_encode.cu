@@ -255,7 +255,8 @@ __device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t 
         const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
         int best = 0x7FFFFFFF;
 #pragma unroll
-        for (int j = 0; j < L; j++) best = min(best, K[j] - (dp4a_uu(p, P[j], 0) << 5));
+        for (int j = 0; j < L; j += 2)  // two entries per 3-input min (VIMNMX3)
+            best = __vimin3_s32(best, K[j] - (dp4a_uu(p, P[j], 0) << 5), K[j + 1] - (dp4a_uu(p, P[j + 1], 0) << 5));
         best += dp4a_uu(p, p, 0) << 4;
         const bool in = (mask >> i) & 1u;
         total += in ? (uint32_t)(best >> 4) : 0u;
@@ -724,7 +725,10 @@ __device__ __forceinline__ uint4 pack_solution(const Shared& S, int tid) {
 
 // ---- kernel ----------------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(NT) bc7_encode_kernel(const __grid_constant__ Params P) {
+#ifndef BC7_MIN_CTAS
+#define BC7_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(NT, BC7_MIN_CTAS) bc7_encode_kernel(const __grid_constant__ Params P) {
     __shared__ Shared S;
     const int tid = threadIdx.x;
     const uint64_t b = (uint64_t)blockIdx.x * NT + tid;

@@ -12,7 +12,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "librosy_tex_cuda.so")
+LIB_PATH = os.environ.get("ROSY_TEX_LIB") or os.path.join(CSRC, "librosy_tex_cuda.so")  # override: A/B builds only
 
 KIND_COLOR, KIND_NORMAL_MAP, KIND_METALLIC_ROUGHNESS, KIND_MIXMAP = 0, 1, 2, 3
 FORMAT_BC7, FORMAT_BC5, FORMAT_BC4 = 0, 1, 2
