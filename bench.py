@@ -8,7 +8,9 @@ step, so 8 GPUs process the config's whole 512-texture set in one step ("scaling
 Mpix = level-0 pixels; every texture additionally carries its 11 smaller levels.
 
 One "step" = one pass of the hot path over the rank's batch:
-  value : inputs already resident in HBM, rosy_tex_encode_device() per texture on one stream,
+  value : inputs already resident in HBM, rosy_tex_encode_batch_device() on one stream (one mip launch
+          for the step's textures, one encoder launch per texture; --per-texture: rosy_tex_mips_device /
+          rosy_tex_blocks_device per texture),
           timed with CUDA events on that stream (barrier + synchronize both sides, max over ranks)
   e2e   : the same batch through the reference-facing C ABI with HOST buffers
           (rosy_tex_submit_rgba8 + rosy_tex_wait_all: pinned H2D, kernels, D2H of the .dds bytes),
@@ -55,6 +57,8 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=2, help="textures in the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
+    ap.add_argument("--per-texture", action="store_true",
+                    help="device leg: one mip launch per texture (rosy_tex_mips_device) instead of the batched call")
     return ap.parse_args()
 
 
@@ -288,9 +292,16 @@ def main():
     d_in = torch.empty((n, in_bytes), dtype=torch.uint8, device=dev)
     for i, img in enumerate(textures):
         d_in[i].copy_(torch.from_numpy(img.reshape(-1)))
-    d_chain = torch.empty(chain_bytes, dtype=torch.uint8, device=dev)
-    d_scratch = torch.zeros(T.device_scratch_size(d), dtype=torch.uint8, device=dev)
-    d_blocks = torch.empty((n, blk_bytes), dtype=torch.uint8, device=dev)
+    # one chain / scratch buffer per texture: the step is ONE batched call (one mip launch for the
+    # whole batch, then one encoder launch per texture)
+    scratch_bytes = T.device_scratch_size(d)
+    chain_pitch = (chain_bytes + 255) // 256 * 256  # device pointers must be 16-byte aligned
+    d_chain = torch.empty((n, chain_pitch), dtype=torch.uint8, device=dev)
+    d_scratch = torch.zeros((n, scratch_bytes), dtype=torch.uint8, device=dev)
+    d_blocks = torch.empty((n, (blk_bytes + 255) // 256 * 256), dtype=torch.uint8, device=dev)
+    d_batch = torch.zeros(T.batch_scratch_size(n), dtype=torch.uint8, device=dev)
+    batch = T.make_batch([(d, d_in[i].data_ptr(), d_chain[i].data_ptr(), d_scratch[i].data_ptr(),
+                           d_blocks[i].data_ptr()) for i in range(n)])
     flush = None
     if n * in_bytes <= L2_BYTES:
         flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
@@ -299,16 +310,27 @@ def main():
     def step(events=None):
         if flush is not None:
             flush.fill_(1)
-        for i in range(n):
-            if events is not None:
-                ea, eb, ec = events[i]
-                ea.record()
-            T.mips_device(d, d_in[i].data_ptr(), d_chain.data_ptr(), d_scratch.data_ptr(), stream)
-            if events is not None:
-                eb.record()
-            T.blocks_device(d, d_in[i].data_ptr(), d_chain.data_ptr(), d_blocks[i].data_ptr(), stream)
-            if events is not None:
-                ec.record()
+        if args.per_texture:
+            for i in range(n):
+                if events is not None:
+                    ea, eb, ec = events[i]
+                    ea.record()
+                T.mips_device(d, d_in[i].data_ptr(), d_chain[i].data_ptr(), d_scratch[i].data_ptr(), stream)
+                if events is not None:
+                    eb.record()
+                T.blocks_device(d, d_in[i].data_ptr(), d_chain[i].data_ptr(), d_blocks[i].data_ptr(), stream)
+                if events is not None:
+                    ec.record()
+            return
+        if events is not None:
+            ea, eb, ec = events[0]
+            ea.record()
+        T.encode_batch_device(batch, d_batch.data_ptr(), stream, True, False)
+        if events is not None:
+            eb.record()
+        T.encode_batch_device(batch, d_batch.data_ptr(), stream, False, True)
+        if events is not None:
+            ec.record()
 
     for _ in range(max(3, args.warmup)):
         step()
@@ -331,8 +353,13 @@ def main():
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
     value = world * mpix_step / (ms_step * 1e-3)
-    mip_ms = float(np.mean([ea.elapsed_time(eb) for evs in kernel_events for (ea, eb, ec) in evs]))
-    enc_ms = float(np.mean([eb.elapsed_time(ec) for evs in kernel_events for (ea, eb, ec) in evs]))
+    # per-launch durations: the batched step has ONE mip launch (all n textures) and n encoder launches
+    used = [evs if args.per_texture else evs[:1] for evs in kernel_events]
+    mip_ms = float(np.mean([ea.elapsed_time(eb) for evs in used for (ea, eb, ec) in evs]))
+    enc_ms = float(np.mean([eb.elapsed_time(ec) for evs in used for (ea, eb, ec) in evs]))
+    mip_tex_per_launch = 1 if args.per_texture else n
+    if not args.per_texture:
+        enc_ms /= n
     clk = clocks.summary()
 
     # ---------------- e2e leg: host buffers through the C ABI work queue --------------------
@@ -370,7 +397,7 @@ def main():
         assert magic == b"DDS ", magic
         # the e2e output must be the same bytes as the device-resident leg produced
         got = np.ctypeslib.as_array(C.cast(host_out[0], C.POINTER(C.c_uint8)), shape=(dds_bytes,))
-        assert (got[T.DDS_HEADER_BYTES:] == d_blocks[0].cpu().numpy()).all(), "e2e and device legs disagree"
+        assert (got[T.DDS_HEADER_BYTES:] == d_blocks[0, :blk_bytes].cpu().numpy()).all(), "e2e and device legs disagree"
         sec = max_over_ranks(sec)
         e2e = {
             "value": world * mpix_step * args.steps / sec,
@@ -396,7 +423,7 @@ def main():
     # algorithmic bytes per launch: mip kernel 4N + 4N/3 (+4N for normal maps, whose level 0
     # is rewritten); encoders read 4 B/px and write 1 (BC7/BC5) or 0.5 (BC4) B/px over 4N/3 px
     chain_px = chain_bytes // 4
-    mip_bytes = 4 * npx + 4 * (chain_px - npx) + (4 * npx if kind == T.KIND_NORMAL_MAP else 0)
+    mip_bytes = (4 * npx + 4 * (chain_px - npx) + (4 * npx if kind == T.KIND_NORMAL_MAP else 0)) * mip_tex_per_launch
     enc_bytes = 4 * chain_px + blk_bytes
     mip_gbs = mip_bytes / (mip_ms * 1e-3) / 1e9
     enc_gbs = enc_bytes / (enc_ms * 1e-3) / 1e9
@@ -434,8 +461,10 @@ def main():
         }
     roofline_mip = {
         "kernel": "mip_fused_kernel", "bound": "hbm", "achieved": mip_gbs, "peak": hbm_peak, "unit": "GB/s",
-        "frac": mip_gbs / hbm_peak, "traffic": prof.get("mip_dram_bytes_per_launch"), "ms_per_launch": mip_ms,
-        "share_of_step": mip_ms * n / ms_step, "algorithmic_bytes_per_launch": mip_bytes, "peak_source": peak_src,
+        "frac": mip_gbs / hbm_peak, "traffic": (prof["mip_dram_bytes_per_texture"] * mip_tex_per_launch if prof.get("mip_dram_bytes_per_texture") else None),
+        "ms_per_launch": mip_ms,
+        "share_of_step": mip_ms * (n // mip_tex_per_launch) / ms_step, "algorithmic_bytes_per_launch": mip_bytes,
+        "textures_per_launch": mip_tex_per_launch, "peak_source": peak_src,
     }
 
     # ---------------- cpu_baseline (rank 0, N = 1 only) ----------------------------------------

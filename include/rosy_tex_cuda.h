@@ -167,7 +167,7 @@ ROSY_TEX_API void* rosy_tex_alloc_host(size_t bytes); /* cudaHostAlloc, portable
 ROSY_TEX_API void rosy_tex_free_host(void* p);
 
 /* ---- device-resident entry points (measurement, callers that already hold device memory) ---
- * All pointers are device pointers on the CURRENT CUDA device; `stream` is a cudaStream_t
+ * All pointers are 16-byte aligned device pointers on the CURRENT CUDA device; `stream` is a cudaStream_t
  * (NULL: legacy default stream).  Nothing synchronises; kernels are only enqueued.
  *   d_chain  : rosy_tex_chain_size() bytes.  Receives levels 1.. (and level 0 for normal maps,
  *              whose level 0 is re-normalised); for colour maps level 0 is read from d_rgba.
@@ -183,6 +183,25 @@ ROSY_TEX_API int rosy_tex_blocks_device(const rosy_tex_desc* desc, const void* d
 ROSY_TEX_API int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba,
                                         void* d_chain, void* d_scratch, void* d_blocks,
                                         void* stream);
+
+/* A batch of device-resident textures ("batched small textures per launch").
+ * The mip chains of every texture whose extents are multiples of 64 are built by ONE kernel
+ * launch per image kind (colour / normal map), so that small textures run at HBM speed instead
+ * of launch latency; the block encoders then run per texture on the same stream.  Pointers as in
+ * rosy_tex_encode_device.  d_batch_scratch: rosy_tex_batch_scratch_size(count) bytes of device
+ * memory, not to be reused before the enqueued work has run.  do_mips / do_blocks select the
+ * stages (both non-zero: the whole hot path). */
+typedef struct rosy_tex_batch_item {
+    rosy_tex_desc desc;
+    const void* d_rgba;
+    void* d_chain;
+    void* d_scratch;
+    void* d_blocks;
+} rosy_tex_batch_item;
+ROSY_TEX_API size_t rosy_tex_batch_scratch_size(int count);
+ROSY_TEX_API int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count,
+                                              void* d_batch_scratch, void* stream, int do_mips,
+                                              int do_blocks);
 
 /* number of kernels this library has launched since load (all threads, all devices) */
 ROSY_TEX_API uint64_t rosy_tex_kernel_launches(void);

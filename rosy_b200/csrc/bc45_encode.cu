@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(NT) bc45_encode_kernel(const __grid_constant__
     const uint32_t bx = lb % lv.bw, by = lb / lv.bw;
     const uint8_t* base = (level == 0 && P.level0) ? P.level0 : P.chainbuf + 4ull * lv.px_offset;
     uint32_t px[16];
-    if (4 * bx + 3 < lv.w && 4 * by + 3 < lv.h && (lv.w & 3u) == 0) {
+    if (4 * bx + 3 < lv.w && 4 * by + 3 < lv.h && (lv.w & 3u) == 0 && ((uintptr_t)base & 15u) == 0) {
 #pragma unroll
         for (int y = 0; y < 4; y++) {
             const uint4 r = __ldg(reinterpret_cast<const uint4*>(

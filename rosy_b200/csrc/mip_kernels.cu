@@ -10,13 +10,20 @@
 // linear premultiplied space for colour, so the result is within 1 LSB of the iterated chain.
 //
 // Two paths:
-//   fused   - ONE launch for the whole chain.  Extents that are multiples of 64 (every config).
-//             Persistent CTAs; each 64x64 RGBA8 tile (16 KB) is brought into shared memory by a
-//             2-D TMA tensor copy (cp.async.bulk.tensor) completing on an mbarrier, 3 stages deep;
-//             the 256 threads read 4x4 texel patches as uint4 rows, reduce levels 1-3 in registers /
-//             shuffles, levels 4-6 in one warp, and the last CTA to finish (atomic ticket) reduces
-//             the per-tile level-6 values down to 1x1.  HBM traffic = the algorithmic 5.33 B/px
-//             (colour) or 9.33 B/px (normal maps, whose level 0 is rewritten).
+//   fused   - ONE launch for the whole chain of one texture, or of a whole batch of textures.
+//             Extents that are multiples of 64 (every config).  Persistent CTAs (2 per SM); each
+//             64x64 RGBA8 tile (16 KB) is brought into shared memory by a 2-D TMA tensor copy
+//             (cp.async.bulk.tensor) completing on an mbarrier, 3 stages deep; the 256 threads read
+//             4x4 texel patches as uint4 rows, reduce levels 1-3 in registers / shuffles, levels 4-6
+//             in one warp, and the CTA that finishes a texture's last tile (atomic ticket) reduces
+//             the per-tile level-6 values down to 1x1 in shared memory.  The kernel is written to
+//             the instruction budget that HBM speed leaves (about 0.9 warp instructions per texel):
+//             sRGB->linear is a bank-replicated (conflict-free) table, linear->sRGB8 a 290-entry
+//             piecewise-linear table over the float's exponent/mantissa bits (no MUFU), fully
+//             opaque warps skip the alpha arithmetic, normal maps are summed as exact packed
+//             16-bit integers, and 8-bit quantisation is a round-down add of 2^23 plus PRMT.
+//             HBM traffic = the algorithmic 5.33 B/px (colour) or 9.33 B/px (normal maps, whose
+//             level 0 is rewritten).
 //   generic - any extent (odd sizes use NVTT-2's polyphase box weights): one small
 //             kernel per level over an fp32 ping-pong scratch.
 #include <cuda.h>
@@ -24,8 +31,10 @@
 #include <math.h>
 #include <stdlib.h>
 #include <stdint.h>
+#include <string.h>
 
 #include <mutex>
+#include <vector>
 
 #include "tex_internal.h"
 
@@ -167,21 +176,60 @@ normal_level0_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, siz
 }
 
 // ------------------------------------------------------------------------------------------
-// fused path: whole chain in one launch, TMA-staged 64x64 tiles
+// fused path: whole chain(s) in one launch, TMA-staged 64x64 tiles
 // ------------------------------------------------------------------------------------------
 constexpr int TILE = 64;
 constexpr int STAGES = 3;
+constexpr int NTHREADS = 256;        // consumer threads (warps 0-7)
+constexpr int NTHREADS_TOTAL = 320;  // + auxiliary warp 8 + producer warp 9
+constexpr int L3_BUFS = 4;           // level-3 hand-over buffers between the consumers and the auxiliary warp
+constexpr int INFO_RING = 16;        // >= STAGES + L3_BUFS + 1 tile descriptors in flight
+constexpr int TAIL_QUEUE = 64;
 constexpr int TILE_BYTES = TILE * TILE * 4;
+constexpr int TAIL_SMEM_PX = 512;  // tail levels with at most this many texels are reduced in shared memory
 
-struct FusedParams {
-    Chain chain;
-    uint8_t* chainbuf;
-    float4* tile_top;   // per-tile level-6 fp32 value, [tiles_y][tiles_x]
-    float4* tail_a;     // ping-pong scratch for the tail levels
+// linear -> sRGB8 as a piecewise-linear table over the float's exponent and top 5 mantissa bits:
+// entry 0 covers [0, 2^-9) (inside the 12.92 c segment), entries 1..288 the 32 slices of each
+// octave [2^-9, 1), entry 289 is c >= 1.  y = slope * c + intercept approximates
+// 255 * toSrgb(c) + 0.5 to better than 0.005 LSB (checked on the host when the table is built).
+constexpr int SRGB_SHIFT = 18;
+constexpr uint32_t SRGB_LO = 0x3B000000u;  // 2^-9
+constexpr uint32_t SRGB_HI = 0x3F800000u;  // 1.0
+constexpr int SRGB_BASE = (int)(SRGB_LO >> SRGB_SHIFT) - 1;
+constexpr int SRGB_ENTRIES = (int)((SRGB_HI - SRGB_LO) >> SRGB_SHIFT) + 2;
+
+__constant__ float2 c_SRGB_ENCODE[SRGB_ENTRIES];
+__constant__ float c_UNORM8[256];  // i / 255.0f, as nvtt::Surface::load produces it
+
+// One texture of a launch.  Lives in kernel parameter space (single texture) or in global memory
+// (batched launch); the tensor map is used in place.
+struct alignas(64) MipTex {
+    CUtensorMap tmap;      // level 0 as a 2-D tensor of 32-bit texels, box 64x64
+    uint8_t* chainbuf;     // RGBA8 levels back to back
+    float4* tile_top;      // per-tile level-6 fp32 value, [tiles_y][tiles_x]
+    float4* tail_a;        // global ping-pong scratch for tail levels too large for shared memory
     float4* tail_b;
-    unsigned int* ticket;
+    unsigned int* ticket;  // tiles finished (returns to 0 when the tail is done)
+    uint32_t w, h;
     int tiles_x, tiles_y;
+    int tile_base;         // first tile of this texture in the launch
+    int levels;
     int normalize;
+    int pad;
+    uint32_t lw[ROSY_TEX_MAX_LEVELS], lh[ROSY_TEX_MAX_LEVELS];
+    uint64_t lpx[ROSY_TEX_MAX_LEVELS];  // px_offset per level
+};
+
+// what the consumers need to know about the tile sitting in a stage; written by the producer
+// thread when it issues the TMA load
+struct TileInfo {
+    uint8_t* chainbuf;
+    float4* tile_top;  // where this tile's level-6 value goes (nullptr: the chain ends at level 6)
+    uint32_t w;
+    int tile_x, tile_y;
+    int tex;
+    int normalize;
+    uint32_t off[8];  // pixel offset of levels 0..6 in the chain buffer (fits 32 bits up to 32768^2)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -216,127 +264,304 @@ __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map,
         "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
         : "memory");
 }
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+// channel C of texel p through the bank-replicated sRGB->linear table; lanebase = shared address
+// of this lane's copy of entry 0 (entries are 128 bytes apart)
+template <int C>
+__device__ __forceinline__ float lin_lookup(uint32_t lanebase, uint32_t p) {
+    return lds_f32(lanebase + (__byte_perm(p, 0u, 0x4440 + C) << 7));
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// ---- colour: linear premultiplied fp32 -> RGBA8 --------------------------------------------
+// 255 * toSrgb(c) + 0.5 through the table, floor taken by a round-down add of 2^23: the low byte
+// of the returned word is the 8-bit value
+__device__ __forceinline__ uint32_t srgb8_bits(float c, const float2* tab /* biased by SRGB_BASE */) {
+    int b = __float_as_int(c);
+    b = max(b, (int)(SRGB_LO - (1u << SRGB_SHIFT)));
+    b = min(b, (int)SRGB_HI);
+    const float2 t = tab[b >> SRGB_SHIFT];
+    return __float_as_uint(__fadd_rd(fmaf(t.x, c, t.y), 8388608.0f));
+}
+// general: v = (linear premultiplied rgb, alpha)
+__device__ __forceinline__ uint32_t finish_colour(float4 v, const float2* tab) {
+    const float ia = v.w > 1e-12f ? rcp_approx(v.w) : 1.0f;  // demultiplyAlpha (epsilon 1e-12)
+    const uint32_t r = srgb8_bits(v.x * ia, tab), g = srgb8_bits(v.y * ia, tab), b = srgb8_bits(v.z * ia, tab);
+    const uint32_t a = __float_as_uint(__fadd_rd(fmaf(v.w, 255.0f, 0.5f), 8388608.0f));
+    const uint32_t rg = __byte_perm(r, g, 0x0040);   // r.b0, g.b0
+    const uint32_t ba = __byte_perm(b, a, 0x0040);   // b.b0, a.b0
+    return __byte_perm(rg, ba, 0x5410);
+}
+// opaque: alpha is exactly 1 everywhere below this texel
+__device__ __forceinline__ uint32_t finish_opaque(float r_, float g_, float b_, const float2* tab) {
+    const uint32_t r = srgb8_bits(r_, tab), g = srgb8_bits(g_, tab), b = srgb8_bits(b_, tab);
+    const uint32_t rg = __byte_perm(r, g, 0x0040);
+    return __byte_perm(rg, b, 0x0410) | 0xFF000000u;
+}
+
+// ---- normal maps ---------------------------------------------------------------------------
+// Surface::normalizeNormalMap on one 8-bit texel (level 0): d = 2 v - 255 exactly, n = d / |d|,
+// out = floor(127.5 n + 128) = floor(255 (n/2 + 1/2) + 0.5); alpha passes through.
+__device__ __forceinline__ uint32_t normalize_texel(uint32_t p) {
+    // bits 0x4B00vv80 = 2^23 + 256 v + 128, minus 2^23 + 32768 = 256 (v - 127.5) = 128 d, exact
+    const float dx = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7504)) - 8421376.0f;
+    const float dy = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7514)) - 8421376.0f;
+    const float dz = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7524)) - 8421376.0f;
+    const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));  // d is odd in every channel: never zero
+    const float s = rsqrtf(l2) * 127.5f;
+    const uint32_t r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
+    const uint32_t g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
+    const uint32_t b = __float_as_uint(__fmaf_rd(dz, s, 8388736.0f));
+    const uint32_t rg = __byte_perm(r, g, 0x0040);
+    return __byte_perm(rg, __byte_perm(b, p, 0x0070), 0x5410);
+}
+// level K texel from exact channel sums over its 4^K level-0 texels, packed rb = r | b << 16 and
+// ga = g | a << 16 (K <= 4 keeps every sum below 2^16)
+template <int K>
+__device__ __forceinline__ uint32_t finish_normal_sums(uint32_t rb, uint32_t ga, int normalize) {
+    constexpr uint32_t half = 1u << (2 * K - 1);
+    if (!normalize) {  // rounded means of all four channels
+        const uint32_t rb8 = ((rb + half * 0x00010001u) >> (2 * K)) & 0x00FF00FFu;
+        const uint32_t ga8 = ((ga + half * 0x00010001u) >> (2 * K)) & 0x00FF00FFu;
+        return rb8 | (ga8 << 8);
+    }
+    // 2^23 + S minus 2^23 + 255 * 4^K / 2 = S - 127.5 * 4^K = (4^K / 2) d, exact; the direction is scale free
+    constexpr float k2 = 8388608.0f + 255.0f * (float)(1 << (2 * K - 1));
+    const float dx = __uint_as_float(__byte_perm(rb, 0x4B000000u, 0x7410)) - k2;
+    const float dz = __uint_as_float(__byte_perm(rb, 0x4B000000u, 0x7432)) - k2;
+    const float dy = __uint_as_float(__byte_perm(ga, 0x4B000000u, 0x7410)) - k2;
+    const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+    const float s = l2 > 0.0f ? rsqrtf(l2) * 127.5f : 0.0f;
+    const uint32_t r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
+    const uint32_t g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
+    const uint32_t b = __float_as_uint(__fmaf_rd(dz, s, 8388736.0f));
+    const uint32_t a = ((ga >> 16) + half) >> (2 * K);
+    const uint32_t rg = __byte_perm(r, g, 0x0040);
+    return __byte_perm(rg, __byte_perm(b, a, 0x0040), 0x5410);
+}
 
 template <bool NORMAL>
-__global__ void __launch_bounds__(256)
-mip_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ FusedParams P) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* tiles = smem;                                            // STAGES x 16 KB
-    float4* l3 = reinterpret_cast<float4*>(smem + STAGES * TILE_BYTES);  // 2 x 64 float4
-    float* lut = reinterpret_cast<float*>(l3 + 128);                  // 256 floats
-    uint64_t* full = reinterpret_cast<uint64_t*>(lut + 256);          // STAGES barriers
-    __shared__ unsigned int s_ticket;
+__device__ __forceinline__ uint32_t finish_any(float4 v, int normalize, const float2* tab) {
+    if (NORMAL) return finish_pixel<true>(v, normalize);
+    return finish_colour(v, tab);
+}
 
-    const int tid = threadIdx.x;
-    const int tx = tid & 15, ty = tid >> 4;
-    const int ntiles = P.tiles_x * P.tiles_y;
-    if (!NORMAL) lut[tid] = c_SRGB_TO_LINEAR[tid];
-    if (tid == 0) {
-        for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap) : "memory");
+// ---- tail: levels 7.. of one texture from its per-tile level-6 values ------------------------
+// Run by the 256 consumer threads (named barrier 1) or, if the request queue overflowed, by the
+// auxiliary warp alone (NT = 32, __syncwarp).
+template <int NT>
+__device__ __forceinline__ void tail_sync() {
+    if (NT == 32)
+        __syncwarp();
+    else
+        asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+}
+
+template <bool NORMAL, int NT, bool GSRC, bool GDST>
+__device__ __forceinline__ void tail_level(const float4* src, int sw, int sh, float4* dst, uint32_t* out,
+                                           int ow, int oh, int normalize, const float2* tab, int tid) {
+    for (int o = tid; o < ow * oh; o += NT) {
+        const int x = o % ow, y = o / ow;
+        int fx, fy;
+        float wx[3], wy[3];
+        const int nx = box_taps(sw, ow, x, fx, wx), ny = box_taps(sh, oh, y, fy, wy);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < ny; j++) {
+            float4 row = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < nx; i++) {
+                const float4* p = src + (size_t)(fy + j) * sw + fx + i;
+                row = fma4(wx[i], GSRC ? __ldcg(p) : *p, row);
+            }
+            acc = fma4(wy[j], row, acc);
+        }
+        if (GDST)
+            __stcg(dst + o, acc);
+        else
+            dst[o] = acc;
+        out[o] = finish_any<NORMAL>(acc, normalize, tab);
     }
-    __syncthreads();
-    // prologue: fill the pipeline
+}
+
+template <bool NORMAL, int NT>
+__device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, const float2* tab, int tid) {
+    __threadfence();  // acquire side of the ticket: other CTAs' tile_top stores are visible
+    const int levels = T->levels, normalize = T->normalize;
+    uint32_t* chain32 = reinterpret_cast<uint32_t*>(T->chainbuf);
+    const float4* gsrc = T->tile_top;
+    float4* gdst = T->tail_a;
+    int sw = T->tiles_x, sh = T->tiles_y;
+    int l = 7;
+    // levels too large for shared memory go through global scratch (L2)
+    for (; l < levels && (int)(T->lw[l] * T->lh[l]) > TAIL_SMEM_PX; l++) {
+        const int ow = (int)T->lw[l], oh = (int)T->lh[l];
+        tail_level<NORMAL, NT, true, true>(gsrc, sw, sh, gdst, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_sync<NT>();
+        gsrc = gdst;
+        gdst = (gdst == T->tail_a) ? T->tail_b : T->tail_a;
+        sw = ow;
+        sh = oh;
+    }
+    if (l < levels) {
+        const int ow = (int)T->lw[l], oh = (int)T->lh[l];
+        tail_level<NORMAL, NT, true, false>(gsrc, sw, sh, sA, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_sync<NT>();
+        sw = ow;
+        sh = oh;
+        l++;
+    }
+    float4 *s = sA, *d = sB;
+    for (; l < levels; l++) {
+        const int ow = (int)T->lw[l], oh = (int)T->lh[l];
+        tail_level<NORMAL, NT, false, false>(s, sw, sh, d, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_sync<NT>();
+        float4* t = s;
+        s = d;
+        d = t;
+        sw = ow;
+        sh = oh;
+    }
+    if (tid == 0) *T->ticket = 0u;  // ready for the next launch
+}
+
+struct FusedSmem {
+    alignas(1024) uint8_t tiles[STAGES][TILE_BYTES];
+    float lin[256 * 32];          // sRGB -> linear / 4, one copy per bank: [value][lane]
+    float4 tailA[TAIL_SMEM_PX];
+    float4 tailB[TAIL_SMEM_PX];
+    float2 srgb[SRGB_ENTRIES + 2];
+    float unorm[256];
+    float4 l3[L3_BUFS][64];       // level-3 values of a tile (colour: fp32; normal: packed integer sums)
+    TileInfo info[INFO_RING];
+    uint64_t full[STAGES];        // TMA landed (1 arrive + tx bytes)
+    uint64_t empty[STAGES];       // every consumer warp holds the tile's texels in registers (8 arrives)
+    uint64_t l3full[L3_BUFS];     // every consumer warp has written its level-3 texels (8 arrives)
+    uint64_t l3empty[L3_BUFS];    // the auxiliary warp has read them (1 arrive)
+    uint64_t aux_done;            // the auxiliary warp has finished its last tile (1 arrive)
+    int queue[TAIL_QUEUE];        // textures whose last tile this CTA finished
+    int nqueue;
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Warp roles (no CTA-wide barrier anywhere in the tile loop):
+//   warps 0-7  consumers: a 4x4 texel patch per thread -> levels 0 (normal maps), 1, 2, 3
+//   warp  8    auxiliary: levels 4-6 of each tile from the level-3 values, per-tile level-6 value,
+//              completion tickets; textures whose last tile it saw are queued for the tail
+//   warp  9    producer: one lane issues the TMA loads, STAGES tiles ahead
+// After the loop the consumers reduce the queued textures' level-6 images down to 1x1.
+template <bool NORMAL>
+__global__ void __launch_bounds__(NTHREADS_TOTAL, 2)
+mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict__ texs,
+                 const int* __restrict__ tile_base, int ntex, int total_tiles) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    FusedSmem& S = *reinterpret_cast<FusedSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float2* tab = S.srgb - SRGB_BASE;
+    const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    if (!NORMAL) {
+        // each warp fills its share of the values, every value replicated across the 32 banks
+        for (int v = warp; v < 256; v += NTHREADS_TOTAL / 32) S.lin[v * 32 + lane] = c_SRGB_TO_LINEAR[v] * 0.25f;
+        for (int i = tid; i < SRGB_ENTRIES; i += NTHREADS_TOTAL) S.srgb[i] = c_SRGB_ENCODE[i];
+    }
+    if (tid < 256) S.unorm[tid] = c_UNORM8[tid];
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
-            const int t = blockIdx.x + s * gridDim.x;
-            if (t < ntiles) {
-                mbar_expect_tx(&full[s], TILE_BYTES);
-                tma_load_tile(tiles + s * TILE_BYTES, &tmap, (t % P.tiles_x) * TILE,
-                              (t / P.tiles_x) * TILE, &full[s]);
-            }
+            mbar_init(&S.full[s], 1);
+            mbar_init(&S.empty[s], 8);
         }
+        for (int b = 0; b < L3_BUFS; b++) {
+            mbar_init(&S.l3full[b], 8);
+            mbar_init(&S.l3empty[b], 1);
+        }
+        mbar_init(&S.aux_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        S.nqueue = 0;
     }
-    const Level L1 = P.chain.lv[1], L2 = P.chain.lv[2], L3 = P.chain.lv[3];
-    uint32_t* c1 = reinterpret_cast<uint32_t*>(P.chainbuf) + L1.px_offset;
-    uint32_t* c2 = reinterpret_cast<uint32_t*>(P.chainbuf) + L2.px_offset;
-    uint32_t* c3 = reinterpret_cast<uint32_t*>(P.chainbuf) + L3.px_offset;
-    int it = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-        const int s = it % STAGES;
-        const int tile_x = t % P.tiles_x, tile_y = t / P.tiles_x;
-        mbar_wait(&full[s], (uint32_t)((it / STAGES) & 1));
-        // each thread owns a 4x4 texel patch: four 16-byte rows
-        const uint4* trow = reinterpret_cast<const uint4*>(tiles + s * TILE_BYTES);
-        uint4 rows[4];
-#pragma unroll
-        for (int r = 0; r < 4; r++) rows[r] = trow[(4 * ty + r) * (TILE / 4) + tx];
-        if (NORMAL) {  // level 0 of a normal map is the re-normalised input
-            uint4* c0 = reinterpret_cast<uint4*>(P.chainbuf);
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                uint4 o;
-                o.x = finish_pixel<true>(load_pixel<true>(rows[r].x, nullptr), P.normalize);
-                o.y = finish_pixel<true>(load_pixel<true>(rows[r].y, nullptr), P.normalize);
-                o.z = finish_pixel<true>(load_pixel<true>(rows[r].z, nullptr), P.normalize);
-                o.w = finish_pixel<true>(load_pixel<true>(rows[r].w, nullptr), P.normalize);
-                const size_t y = (size_t)tile_y * TILE + 4 * ty + r;
-                c0[(y * P.chain.lv[0].w + (size_t)tile_x * TILE) / 4 + tx] = o;
+    __syncthreads();
+
+    if (warp == 9) {
+        // ================================ producer ================================
+        if (lane != 0) return;
+        int cur = 0;  // texture cursor: tiles are visited in increasing order
+        for (int it = 0; it < my_tiles; it++) {
+            const int t = (int)blockIdx.x + it * (int)gridDim.x;
+            const int s = it % STAGES;
+            if (it >= STAGES) mbar_wait(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
+            const MipTex* T = &single;
+            if (texs) {
+                while (cur + 1 < ntex && t >= tile_base[cur + 1]) cur++;
+                T = texs + cur;
             }
-        }
-        // level 1: 2x2 per thread
-        float4 q[2][2];
+            const int lt = t - T->tile_base;
+            const int tiles_x = T->tiles_x;
+            const int tile_x = lt % tiles_x, tile_y = lt / tiles_x;
+            TileInfo& I = S.info[it % INFO_RING];
+            I.chainbuf = T->chainbuf;
+            I.tile_top = T->levels > 7 ? T->tile_top + (size_t)tile_y * tiles_x + tile_x : nullptr;
+            I.w = T->w;
+            I.tile_x = tile_x;
+            I.tile_y = tile_y;
+            I.tex = cur;
+            I.normalize = T->normalize;
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-            const uint4 a = rows[2 * j], b = rows[2 * j + 1];
-            q[j][0] = scale4(add4(add4(load_pixel<NORMAL>(a.x, lut), load_pixel<NORMAL>(a.y, lut)),
-                                  add4(load_pixel<NORMAL>(b.x, lut), load_pixel<NORMAL>(b.y, lut))),
-                             0.25f);
-            q[j][1] = scale4(add4(add4(load_pixel<NORMAL>(a.z, lut), load_pixel<NORMAL>(a.w, lut)),
-                                  add4(load_pixel<NORMAL>(b.z, lut), load_pixel<NORMAL>(b.w, lut))),
-                             0.25f);
+            for (int l = 0; l < 7; l++) I.off[l] = (uint32_t)T->lpx[l];
+            mbar_expect_tx(&S.full[s], TILE_BYTES);
+            tma_load_tile(S.tiles[s], &T->tmap, tile_x * TILE, tile_y * TILE, &S.full[s]);
         }
-#pragma unroll
-        for (int j = 0; j < 2; j++) {
-            const size_t y = (size_t)tile_y * 32 + 2 * ty + j;
-            uint2 o = make_uint2(finish_pixel<NORMAL>(q[j][0], P.normalize),
-                                 finish_pixel<NORMAL>(q[j][1], P.normalize));
-            *reinterpret_cast<uint2*>(c1 + y * L1.w + (size_t)tile_x * 32 + 2 * tx) = o;
-        }
-        // level 2: one texel per thread
-        float4 v2 = scale4(add4(add4(q[0][0], q[0][1]), add4(q[1][0], q[1][1])), 0.25f);
-        c2[((size_t)tile_y * 16 + ty) * L2.w + (size_t)tile_x * 16 + tx] =
-            finish_pixel<NORMAL>(v2, P.normalize);
-        // level 3: 2x2 threads (lane ^ 1 = tx neighbour, lane ^ 16 = ty neighbour)
-        float4 v3 = v2;
-        v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 1);
-        v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 1);
-        v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 1);
-        v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 1);
-        v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 16);
-        v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 16);
-        v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 16);
-        v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 16);
-        v3 = scale4(v3, 0.25f);
-        float4* l3buf = l3 + (it & 1) * 64;
-        if (((tx | ty) & 1) == 0) {
-            const int x3 = tx >> 1, y3 = ty >> 1;
-            l3buf[y3 * 8 + x3] = v3;
-            c3[((size_t)tile_y * 8 + y3) * L3.w + (size_t)tile_x * 8 + x3] =
-                finish_pixel<NORMAL>(v3, P.normalize);
-        }
-        __syncthreads();  // every thread has consumed stage s; level-3 values are visible
-        if (tid == 0) {
-            const int tn = t + STAGES * gridDim.x;
-            if (tn < ntiles) {
-                mbar_expect_tx(&full[s], TILE_BYTES);
-                tma_load_tile(tiles + s * TILE_BYTES, &tmap, (tn % P.tiles_x) * TILE,
-                              (tn / P.tiles_x) * TILE, &full[s]);
+        return;
+    }
+
+    if (warp == 8) {
+        // ================================ auxiliary ================================
+        const int l16 = lane & 15;  // lanes 16..31 mirror 0..15
+        const int x4 = l16 & 3, y4 = l16 >> 2;
+        int run_tex = -1, run_cnt = 0;  // tiles finished since the last ticket update (lane 0)
+        auto flush_ticket = [&]() {
+            // lane 0: publish run_cnt finished tiles of texture run_tex; queue the tail if they were the last
+            const MipTex* T = texs ? texs + run_tex : &single;
+            __threadfence();  // release: this thread's tile_top stores
+            const unsigned done = atomicAdd(T->ticket, (unsigned)run_cnt) + (unsigned)run_cnt;
+            return done == (unsigned)(T->tiles_x * T->tiles_y);
+        };
+        for (int it = 0; it < my_tiles; it++) {
+            const int b = it % L3_BUFS;
+            mbar_wait(&S.l3full[b], (uint32_t)((it / L3_BUFS) & 1));
+            const TileInfo I = S.info[it % INFO_RING];
+            uint32_t* chain32 = reinterpret_cast<uint32_t*>(I.chainbuf);
+            const float4* l3buf = S.l3[b];
+            float4 v4;
+            uint32_t px4;
+            if (NORMAL) {
+                const uint2* q = reinterpret_cast<const uint2*>(l3buf);
+                const uint2 a = q[(2 * y4) * 8 + 2 * x4], bq = q[(2 * y4) * 8 + 2 * x4 + 1];
+                const uint2 c = q[(2 * y4 + 1) * 8 + 2 * x4], d = q[(2 * y4 + 1) * 8 + 2 * x4 + 1];
+                const uint32_t rb4 = a.x + bq.x + c.x + d.x, ga4 = a.y + bq.y + c.y + d.y;  // <= 65280 per lane
+                px4 = finish_normal_sums<4>(rb4, ga4, I.normalize);
+                // from here on fp32 means in [0,1]: exact integers scaled once
+                const float k = 1.0f / (256.0f * 255.0f);
+                v4 = make_float4((float)(rb4 & 0xFFFFu) * k, (float)(ga4 & 0xFFFFu) * k, (float)(rb4 >> 16) * k,
+                                 (float)(ga4 >> 16) * k);
+            } else {
+                v4 = scale4(add4(add4(l3buf[(2 * y4) * 8 + 2 * x4], l3buf[(2 * y4) * 8 + 2 * x4 + 1]),
+                                 add4(l3buf[(2 * y4 + 1) * 8 + 2 * x4], l3buf[(2 * y4 + 1) * 8 + 2 * x4 + 1])),
+                            0.25f);
+                px4 = finish_colour(v4, tab);
             }
-        }
-        if (tid < 32) {  // levels 4, 5, 6 of this tile in one warp
-            const int lane = tid & 15;  // lanes 16..31 mirror 0..15
-            const int x4 = lane & 3, y4 = lane >> 2;
-            float4 v4 = scale4(add4(add4(l3buf[(2 * y4) * 8 + 2 * x4], l3buf[(2 * y4) * 8 + 2 * x4 + 1]),
-                                    add4(l3buf[(2 * y4 + 1) * 8 + 2 * x4],
-                                         l3buf[(2 * y4 + 1) * 8 + 2 * x4 + 1])),
-                               0.25f);
-            const Level L4 = P.chain.lv[4], L5 = P.chain.lv[5], L6 = P.chain.lv[6];
-            uint32_t* cb = reinterpret_cast<uint32_t*>(P.chainbuf);
-            if (tid < 16)
-                cb[L4.px_offset + ((size_t)tile_y * 4 + y4) * L4.w + (size_t)tile_x * 4 + x4] =
-                    finish_pixel<NORMAL>(v4, P.normalize);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.l3empty[b]);  // the level-3 buffer may be overwritten
+            const uint32_t w4 = I.w >> 4, w5 = I.w >> 5, w6 = I.w >> 6;
+            if (lane < 16) chain32[I.off[4] + (size_t)(I.tile_y * 4 + y4) * w4 + I.tile_x * 4 + x4] = px4;
             float4 v5 = v4;
             v5.x += __shfl_xor_sync(0xFFFFFFFFu, v5.x, 1);
             v5.y += __shfl_xor_sync(0xFFFFFFFFu, v5.y, 1);
@@ -347,9 +572,9 @@ mip_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             v5.z += __shfl_xor_sync(0xFFFFFFFFu, v5.z, 4);
             v5.w += __shfl_xor_sync(0xFFFFFFFFu, v5.w, 4);
             v5 = scale4(v5, 0.25f);
-            if (tid < 16 && ((x4 | y4) & 1) == 0)
-                cb[L5.px_offset + ((size_t)tile_y * 2 + (y4 >> 1)) * L5.w + (size_t)tile_x * 2 + (x4 >> 1)] =
-                    finish_pixel<NORMAL>(v5, P.normalize);
+            if (lane < 16 && ((x4 | y4) & 1) == 0)
+                chain32[I.off[5] + (size_t)(I.tile_y * 2 + (y4 >> 1)) * w5 + I.tile_x * 2 + (x4 >> 1)] =
+                    finish_any<NORMAL>(v5, I.normalize, tab);
             float4 v6 = v5;
             v6.x += __shfl_xor_sync(0xFFFFFFFFu, v6.x, 2);
             v6.y += __shfl_xor_sync(0xFFFFFFFFu, v6.y, 2);
@@ -360,49 +585,192 @@ mip_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             v6.z += __shfl_xor_sync(0xFFFFFFFFu, v6.z, 8);
             v6.w += __shfl_xor_sync(0xFFFFFFFFu, v6.w, 8);
             v6 = scale4(v6, 0.25f);
-            if (tid == 0) {
-                cb[L6.px_offset + (size_t)tile_y * L6.w + tile_x] = finish_pixel<NORMAL>(v6, P.normalize);
-                P.tile_top[(size_t)tile_y * P.tiles_x + tile_x] = v6;
+            // ticket bookkeeping is warp-uniform (every lane reads the same TileInfo); lane 0 acts
+            const bool has_tail = I.tile_top != nullptr;
+            int overflow_tex = -1;
+            if (run_tex >= 0 && run_tex != I.tex) {
+                if (lane == 0 && flush_ticket()) {
+                    if (S.nqueue < TAIL_QUEUE)
+                        S.queue[S.nqueue++] = run_tex;
+                    else
+                        overflow_tex = run_tex;
+                }
+                run_tex = -1;
+                run_cnt = 0;
+            }
+            overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
+            if (overflow_tex >= 0)
+                run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane);
+            if (lane == 0) {
+                chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = finish_any<NORMAL>(v6, I.normalize, tab);
+                if (has_tail) __stcg(I.tile_top, v6);
+            }
+            if (has_tail) {
+                run_tex = I.tex;
+                run_cnt++;
             }
         }
-    }
-    // ---- tail: the last CTA to finish reduces the per-tile values (level 6) down to 1x1 ----
-    if (P.chain.levels <= 7) return;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_ticket = atomicAdd(P.ticket, 1u);
-    __syncthreads();
-    if (s_ticket != gridDim.x - 1) return;
-    __threadfence();
-    const float4* src = P.tile_top;
-    float4* dst = P.tail_a;
-    int sw = P.tiles_x, sh = P.tiles_y;
-    for (int l = 7; l < P.chain.levels; l++) {
-        const Level L = P.chain.lv[l];
-        uint32_t* out = reinterpret_cast<uint32_t*>(P.chainbuf) + L.px_offset;
-        for (int o = tid; o < (int)(L.w * L.h); o += 256) {
-            const int x = o % (int)L.w, y = o / (int)L.w;
-            int fx, fy;
-            float wx[3], wy[3];
-            const int nx = box_taps(sw, (int)L.w, x, fx, wx), ny = box_taps(sh, (int)L.h, y, fy, wy);
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int j = 0; j < ny; j++) {
-                float4 row = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int i = 0; i < nx; i++)
-                    row = fma4(wx[i], __ldcg(src + (size_t)(fy + j) * sw + fx + i), row);
-                acc = fma4(wy[j], row, acc);
-            }
-            dst[o] = acc;
-            out[o] = finish_pixel<NORMAL>(acc, P.normalize);
+        int overflow_tex = -1;
+        if (run_tex >= 0 && lane == 0 && flush_ticket()) {
+            if (S.nqueue < TAIL_QUEUE)
+                S.queue[S.nqueue++] = run_tex;
+            else
+                overflow_tex = run_tex;
         }
-        __threadfence();
-        __syncthreads();
-        src = dst;
-        dst = (dst == P.tail_a) ? P.tail_b : P.tail_a;
-        sw = (int)L.w;
-        sh = (int)L.h;
+        overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
+        if (overflow_tex >= 0)
+            run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&S.aux_done);
+        return;
     }
-    if (tid == 0) *P.ticket = 0u;  // ready for the next launch
+
+    // ================================ consumers ================================
+    const int tx = tid & 15, ty = tid >> 4;
+    const bool l3_owner = ((tx | ty) & 1) == 0;
+    const uint32_t lb = smem_u32(S.lin + lane);
+    for (int it = 0; it < my_tiles; it++) {
+        const int s = it % STAGES;
+        mbar_wait(&S.full[s], (uint32_t)((it / STAGES) & 1));
+        // each thread owns a 4x4 texel patch: four 16-byte rows
+        const uint4* trow = reinterpret_cast<const uint4*>(S.tiles[s]);
+        uint4 rows[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) rows[r] = trow[(4 * ty + r) * (TILE / 4) + tx];
+        const TileInfo& I = S.info[it % INFO_RING];
+        uint32_t* chain32 = reinterpret_cast<uint32_t*>(I.chainbuf);
+        const int tile_x = I.tile_x, tile_y = I.tile_y, normalize = I.normalize;
+        const uint32_t w0 = I.w, w1 = w0 >> 1, w2 = w0 >> 2, w3 = w0 >> 3;
+        uint32_t* c1 = chain32 + I.off[1] + (size_t)(tile_y * 32 + 2 * ty) * w1 + tile_x * 32 + 2 * tx;
+        uint32_t* c2 = chain32 + I.off[2] + (size_t)(tile_y * 16 + ty) * w2 + tile_x * 16 + tx;
+        uint32_t* c3 = chain32 + I.off[3] + (size_t)(tile_y * 8 + (ty >> 1)) * w3 + tile_x * 8 + (tx >> 1);
+        uint4* c0 = reinterpret_cast<uint4*>(chain32 + I.off[0] + (size_t)(tile_y * TILE + 4 * ty) * w0 + tile_x * TILE) + tx;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&S.empty[s]);  // the texels are in registers: the stage may be refilled
+        const int b = it % L3_BUFS;
+        float4* l3buf = S.l3[b];
+
+        if (NORMAL) {
+            // level 0 of a normal map is the re-normalised input (Packager.cpp:294-296 at mip 0)
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                uint4 o = rows[r];
+                if (normalize) {
+                    o.x = normalize_texel(o.x);
+                    o.y = normalize_texel(o.y);
+                    o.z = normalize_texel(o.z);
+                    o.w = normalize_texel(o.w);
+                }
+                c0[(size_t)r * (w0 / 4)] = o;
+            }
+            // exact integer channel sums, two 16-bit lanes per word
+            uint32_t rb2 = 0, ga2 = 0;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+                const uint32_t rb_l = (a.x & 0x00FF00FFu) + (a.y & 0x00FF00FFu) + (bq.x & 0x00FF00FFu) + (bq.y & 0x00FF00FFu);
+                const uint32_t ga_l = ((a.x >> 8) & 0x00FF00FFu) + ((a.y >> 8) & 0x00FF00FFu) +
+                                      ((bq.x >> 8) & 0x00FF00FFu) + ((bq.y >> 8) & 0x00FF00FFu);
+                const uint32_t rb_r = (a.z & 0x00FF00FFu) + (a.w & 0x00FF00FFu) + (bq.z & 0x00FF00FFu) + (bq.w & 0x00FF00FFu);
+                const uint32_t ga_r = ((a.z >> 8) & 0x00FF00FFu) + ((a.w >> 8) & 0x00FF00FFu) +
+                                      ((bq.z >> 8) & 0x00FF00FFu) + ((bq.w >> 8) & 0x00FF00FFu);
+                *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
+                    make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
+                rb2 += rb_l + rb_r;
+                ga2 += ga_l + ga_r;
+            }
+            *c2 = finish_normal_sums<2>(rb2, ga2, normalize);
+            uint32_t rb3 = rb2, ga3 = ga2;
+            rb3 += __shfl_xor_sync(0xFFFFFFFFu, rb3, 1);
+            ga3 += __shfl_xor_sync(0xFFFFFFFFu, ga3, 1);
+            rb3 += __shfl_xor_sync(0xFFFFFFFFu, rb3, 16);
+            ga3 += __shfl_xor_sync(0xFFFFFFFFu, ga3, 16);
+            if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
+            if (l3_owner) {
+                *c3 = finish_normal_sums<3>(rb3, ga3, normalize);
+                reinterpret_cast<uint2*>(l3buf)[(ty >> 1) * 8 + (tx >> 1)] = make_uint2(rb3, ga3);
+            }
+        } else {
+            uint32_t all = rows[0].x & rows[0].y & rows[0].z & rows[0].w;
+#pragma unroll
+            for (int r = 1; r < 4; r++) all &= rows[r].x & rows[r].y & rows[r].z & rows[r].w;
+            const bool opaque = __all_sync(0xFFFFFFFFu, all >= 0xFF000000u);
+            float4 v2;
+            if (opaque) {
+                float sr = 0.f, sg = 0.f, sb = 0.f;
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+                    uint32_t o[2];
+#pragma unroll
+                    for (int i = 0; i < 2; i++) {
+                        const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
+                        const float r_ = (lin_lookup<0>(lb, p0) + lin_lookup<0>(lb, p1)) + (lin_lookup<0>(lb, p2) + lin_lookup<0>(lb, p3));
+                        const float g_ = (lin_lookup<1>(lb, p0) + lin_lookup<1>(lb, p1)) + (lin_lookup<1>(lb, p2) + lin_lookup<1>(lb, p3));
+                        const float b_ = (lin_lookup<2>(lb, p0) + lin_lookup<2>(lb, p1)) + (lin_lookup<2>(lb, p2) + lin_lookup<2>(lb, p3));
+                        o[i] = finish_opaque(r_, g_, b_, tab);
+                        sr += r_;
+                        sg += g_;
+                        sb += b_;
+                    }
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                }
+                v2 = make_float4(sr * 0.25f, sg * 0.25f, sb * 0.25f, 1.0f);
+                *c2 = finish_opaque(v2.x, v2.y, v2.z, tab);
+            } else {
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+                    uint32_t o[2];
+#pragma unroll
+                    for (int i = 0; i < 2; i++) {
+                        const uint32_t p[4] = {i ? a.z : a.x, i ? a.w : a.y, i ? bq.z : bq.x, i ? bq.w : bq.y};
+                        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const float al = S.unorm[p[k] >> 24];
+                            q.x = fmaf(lin_lookup<0>(lb, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
+                            q.y = fmaf(lin_lookup<1>(lb, p[k]), al, q.y);
+                            q.z = fmaf(lin_lookup<2>(lb, p[k]), al, q.z);
+                            q.w += al;
+                        }
+                        q.w *= 0.25f;
+                        o[i] = finish_colour(q, tab);
+                        sum = add4(sum, q);
+                    }
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                }
+                v2 = scale4(sum, 0.25f);
+                *c2 = finish_colour(v2, tab);
+            }
+            // level 3: 2x2 threads (lane ^ 1 = tx neighbour, lane ^ 16 = ty neighbour)
+            float4 v3 = v2;
+            v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 1);
+            v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 1);
+            v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 1);
+            v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 1);
+            v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 16);
+            v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 16);
+            v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 16);
+            v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 16);
+            v3 = scale4(v3, 0.25f);
+            if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
+            if (l3_owner) {
+                l3buf[(ty >> 1) * 8 + (tx >> 1)] = v3;
+                *c3 = finish_colour(v3, tab);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&S.l3full[b]);
+    }
+    // ---- tails of the textures whose last tile was finished by this CTA ----
+    mbar_wait(&S.aux_done, 0u);
+    const int nq = S.nqueue;
+    for (int k = 0; k < nq; k++) {
+        run_tail<NORMAL, 256>(texs ? texs + S.queue[k] : &single, S.tailA, S.tailB, tab, tid);
+        tail_sync<256>();
+    }
 }
 
 // ---- host side ----------------------------------------------------------------------------
@@ -424,83 +792,131 @@ encode_tiled_fn get_encode_tiled() {
     return fn;
 }
 
-constexpr size_t FUSED_SMEM = STAGES * TILE_BYTES + 128 * sizeof(float4) + 256 * sizeof(float) +
-                              STAGES * sizeof(uint64_t);
-
 bool fused_ok(const Chain& c) {
     return c.lv[0].w % TILE == 0 && c.lv[0].h % TILE == 0 && c.levels >= 7;
 }
 
 size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+int force_generic() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ROSY_TEX_MIPS");
+        v = (e && e[0] == 'g') ? 1 : 0;
+    }
+    return v;
+}
+
+// describe one texture for the fused kernel; false if the tensor map cannot be built
+bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba, uint8_t* d_chain,
+                 void* d_scratch, int tile_base) {
+    memset(&T, 0, sizeof T);
+    const cuuint64_t dims[2] = {c.lv[0].w, c.lv[0].h};
+    const cuuint64_t strides[1] = {(cuuint64_t)c.lv[0].w * 4};
+    const cuuint32_t box[2] = {TILE, TILE};
+    const cuuint32_t estr[2] = {1, 1};
+    if (get_encode_tiled()(&T.tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint8_t*>(d_rgba), dims, strides,
+                           box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    T.chainbuf = d_chain;
+    T.w = c.lv[0].w;
+    T.h = c.lv[0].h;
+    T.tiles_x = (int)(c.lv[0].w / TILE);
+    T.tiles_y = (int)(c.lv[0].h / TILE);
+    T.tile_base = tile_base;
+    T.levels = c.levels;
+    T.normalize = normalize;
+    const size_t ntiles = (size_t)T.tiles_x * T.tiles_y;
+    uint8_t* sc = reinterpret_cast<uint8_t*>(d_scratch);
+    T.ticket = reinterpret_cast<unsigned int*>(sc);
+    T.tile_top = reinterpret_cast<float4*>(sc + 256);
+    T.tail_a = T.tile_top + ntiles;
+    T.tail_b = T.tail_a + ntiles;
+    for (int l = 0; l < c.levels; l++) {
+        T.lw[l] = c.lv[l].w;
+        T.lh[l] = c.lv[l].h;
+        T.lpx[l] = c.lv[l].px_offset;
+    }
+    return true;
+}
+
+template <bool NORMAL>
+cudaError_t launch_fused(const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
+                         int total_tiles, cudaStream_t s) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(mip_fused_kernel<NORMAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(FusedSmem));
+    });
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = total_tiles < 2 * sms ? total_tiles : 2 * sms;
+    mip_fused_kernel<NORMAL><<<grid, NTHREADS_TOTAL, sizeof(FusedSmem), s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
+    return cudaGetLastError();
+}
+
 }  // namespace
 
-static int g_force_generic = -1;
-
 size_t mips_scratch_bytes(const Chain& c) {
-    // generic: fp32 level 1 + fp32 level 2 (ping-pong);  fused: tile tops + two tail buffers + ticket
+    // generic: fp32 level 1 + fp32 level 2 (ping-pong);  fused: ticket + tile tops + two tail buffers
     const size_t l1 = c.levels > 1 ? (size_t)c.lv[1].w * c.lv[1].h * sizeof(float4) : 0;
     const size_t l2 = c.levels > 2 ? (size_t)c.lv[2].w * c.lv[2].h * sizeof(float4) : 0;
     const size_t generic = align256(l1) + align256(l2) + 256;
     const size_t ntiles = (size_t)((c.lv[0].w + TILE - 1) / TILE) * ((c.lv[0].h + TILE - 1) / TILE);
     const size_t fused = 256 + 3 * ntiles * sizeof(float4);
-    return generic > fused ? generic : fused;
+    return align256(generic > fused ? generic : fused);
 }
+
+size_t mips_batch_desc_bytes(int n) { return align256((size_t)n * sizeof(MipTex)) + align256((size_t)(n + 1) * sizeof(int)); }
 
 int mips_upload_tables() {
-    float lut[256];
+    float lut[256], unorm[256];
     for (int i = 0; i < 256; i++) {
-        // Surface::toLinearFromSrgb (row A5) of i/255, computed in fp32 like the reference's surface
+        // Surface::load then Surface::toLinearFromSrgb (row A5) of i/255, in fp32 like the reference's surface
         const float c = (float)i / 255.0f;
+        unorm[i] = c;
         lut[i] = c <= 0.04045f ? c / 12.92f : powf((c + 0.055f) / 1.055f, 2.4f);
     }
-    return cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess ? 0 : -1;
+    // Surface::toSrgb (row A5; NVTT-2's literal exponent 0.41666f) followed by compress()'s
+    // quantisation, y(c) = 255 s(c) + 0.5, as one line per slice of the float range
+    static float2 enc[SRGB_ENTRIES];
+    auto y = [](double c) {
+        const double s = c <= (double)0.0031308f ? (double)12.92f * c : (double)1.055f * pow(c, (double)0.41666f) - (double)0.055f;
+        return 255.0 * (s < 0.0 ? 0.0 : (s > 1.0 ? 1.0 : s)) + 0.5;
+    };
+    enc[0] = make_float2(12.92f * 255.0f, 0.5f);
+    double worst = 0.0;
+    for (int e = 1; e < SRGB_ENTRIES - 1; e++) {
+        const uint32_t b0 = SRGB_LO + ((uint32_t)(e - 1) << SRGB_SHIFT), b1 = b0 + (1u << SRGB_SHIFT);
+        float f0, f1;
+        memcpy(&f0, &b0, 4);
+        memcpy(&f1, &b1, 4);
+        const double c0 = f0, c1 = f1, slope = (y(c1) - y(c0)) / (c1 - c0);
+        double lo = 0.0, hi = 0.0;  // deviation of y from the chord
+        for (int k = 0; k <= 64; k++) {
+            const double c = c0 + (c1 - c0) * k / 64.0, d = y(c) - (y(c0) + slope * (c - c0));
+            lo = d < lo ? d : lo;
+            hi = d > hi ? d : hi;
+        }
+        const double shift = 0.5 * (lo + hi);
+        enc[e] = make_float2((float)slope, (float)(y(c0) - slope * c0 + shift));
+        worst = fmax(worst, 0.5 * (hi - lo));
+    }
+    enc[SRGB_ENTRIES - 1] = make_float2(0.0f, 255.5f);
+    if (worst > 0.01) return -1;  // table must stay far inside the 1 LSB bar
+    return cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
+                   cudaMemcpyToSymbol(c_UNORM8, unorm, sizeof unorm) == cudaSuccess &&
+                   cudaMemcpyToSymbol(c_SRGB_ENCODE, enc, sizeof enc) == cudaSuccess
+               ? 0
+               : -1;
 }
 
-int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
-                uint8_t* d_chain, void* d_scratch, cudaStream_t s) {
-    if (g_force_generic < 0) {
-        const char* e = getenv("ROSY_TEX_MIPS");
-        g_force_generic = (e && e[0] == 'g') ? 1 : 0;
-    }
+static int launch_mips_generic(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
+                               uint8_t* d_chain, void* d_scratch, cudaStream_t s) {
     int launches = 0;
     const size_t npx0 = (size_t)c.lv[0].w * c.lv[0].h;
-    if (fused_ok(c) && !g_force_generic && get_encode_tiled()) {
-        CUtensorMap tmap;
-        const cuuint64_t dims[2] = {c.lv[0].w, c.lv[0].h};
-        const cuuint64_t strides[1] = {(cuuint64_t)c.lv[0].w * 4};
-        const cuuint32_t box[2] = {TILE, TILE};
-        const cuuint32_t estr[2] = {1, 1};
-        CUresult r = get_encode_tiled()(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint8_t*>(d_rgba),
-                                        dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return -1;
-        FusedParams P;
-        P.chain = c;
-        P.chainbuf = d_chain;
-        P.tiles_x = (int)(c.lv[0].w / TILE);
-        P.tiles_y = (int)(c.lv[0].h / TILE);
-        P.normalize = normalize;
-        const size_t ntiles = (size_t)P.tiles_x * P.tiles_y;
-        uint8_t* sc = reinterpret_cast<uint8_t*>(d_scratch);
-        P.ticket = reinterpret_cast<unsigned int*>(sc);
-        P.tile_top = reinterpret_cast<float4*>(sc + 256);
-        P.tail_a = P.tile_top + ntiles;
-        P.tail_b = P.tail_a + ntiles;
-        int dev = 0, sms = 148;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const unsigned grid = (unsigned)(ntiles < (size_t)(3 * sms) ? ntiles : (size_t)(3 * sms));
-        cudaFuncSetAttribute(mip_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM);
-        cudaFuncSetAttribute(mip_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM);
-        if (normal_map)
-            mip_fused_kernel<true><<<grid, 256, FUSED_SMEM, s>>>(tmap, P);
-        else
-            mip_fused_kernel<false><<<grid, 256, FUSED_SMEM, s>>>(tmap, P);
-        return cudaGetLastError() == cudaSuccess ? 1 : -1;
-    }
-    // ---- generic path ----
     if (normal_map) {
         const size_t n4 = npx0 / 4;
         normal_level0_kernel<<<(unsigned)((n4 + 1 + 255) / 256), 256, 0, s>>>(
@@ -531,6 +947,67 @@ int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d
         launches++;
     }
     return cudaGetLastError() == cudaSuccess ? launches : -1;
+}
+
+int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
+                uint8_t* d_chain, void* d_scratch, cudaStream_t s) {
+    if (fused_ok(c) && !force_generic() && get_encode_tiled()) {
+        MipTex T;
+        if (!fill_miptex(T, c, normalize, d_rgba, d_chain, d_scratch, 0)) return -1;
+        const int ntiles = T.tiles_x * T.tiles_y;
+        const cudaError_t e = normal_map ? launch_fused<true>(&T, nullptr, nullptr, 1, ntiles, s)
+                                         : launch_fused<false>(&T, nullptr, nullptr, 1, ntiles, s);
+        return e == cudaSuccess ? 1 : -1;
+    }
+    return launch_mips_generic(c, normal_map, normalize, d_rgba, d_chain, d_scratch, s);
+}
+
+// Mip chains of n textures: ONE fused launch per image kind present for every texture the fused
+// kernel accepts, the per-level kernels for the rest.  d_desc: mips_batch_desc_bytes(n) bytes of
+// device memory that must stay untouched until the launch has run.
+int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream_t s) {
+    int launches = 0;
+    std::vector<MipTex> texs;
+    std::vector<int> base;
+    uint8_t* dd = reinterpret_cast<uint8_t*>(d_desc);
+    size_t used = 0;  // descriptors of the two kinds sit one after the other in d_desc
+    for (int kind = 0; kind < 2; kind++) {
+        texs.clear();
+        base.clear();
+        int total = 0;
+        for (int i = 0; i < n; i++) {
+            const MipBatchItem& it = items[i];
+            if ((int)it.normal_map != kind) continue;
+            if (!(fused_ok(it.chain) && !force_generic() && get_encode_tiled())) continue;
+            MipTex T;
+            if (!fill_miptex(T, it.chain, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, total)) return -1;
+            base.push_back(total);
+            total += T.tiles_x * T.tiles_y;
+            texs.push_back(T);
+        }
+        if (texs.empty()) continue;
+        base.push_back(total);
+        const size_t tb = align256(texs.size() * sizeof(MipTex)), bb = align256(base.size() * sizeof(int));
+        MipTex* d_texs = reinterpret_cast<MipTex*>(dd + used);
+        int* d_base = reinterpret_cast<int*>(dd + used + tb);
+        used += tb + bb;
+        if (cudaMemcpyAsync(d_texs, texs.data(), texs.size() * sizeof(MipTex), cudaMemcpyHostToDevice, s) != cudaSuccess ||
+            cudaMemcpyAsync(d_base, base.data(), base.size() * sizeof(int), cudaMemcpyHostToDevice, s) != cudaSuccess)
+            return -1;
+        const cudaError_t e = kind ? launch_fused<true>(&texs[0], d_texs, d_base, (int)texs.size(), total, s)
+                                   : launch_fused<false>(&texs[0], d_texs, d_base, (int)texs.size(), total, s);
+        if (e != cudaSuccess) return -1;
+        launches++;
+    }
+    for (int i = 0; i < n; i++) {
+        const MipBatchItem& it = items[i];
+        if (fused_ok(it.chain) && !force_generic() && get_encode_tiled()) continue;
+        if (it.chain.levels <= 1 && !it.normal_map) continue;
+        const int k = launch_mips_generic(it.chain, it.normal_map, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, s);
+        if (k < 0) return -1;
+        launches += k;
+    }
+    return launches;
 }
 
 }  // namespace rosy_tex

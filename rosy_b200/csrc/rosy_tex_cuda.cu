@@ -665,6 +665,10 @@ size_t rosy_tex_device_scratch_size(const rosy_tex_desc* desc) {
     return mips_scratch_bytes(make_chain(r.w, r.h));
 }
 
+static bool misaligned(const void* a, const void* b, const void* c, const void* d) {
+    return (((uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)d) & 15u) != 0;
+}
+
 static int device_common(const rosy_tex_desc* desc, Resolved& r) {
     int rc = ensure_init();
     if (rc) return rc;
@@ -681,6 +685,7 @@ int rosy_tex_mips_device(const rosy_tex_desc* desc, const void* d_rgba, void* d_
     int rc = device_common(desc, r);
     if (rc) return rc;
     if (!d_rgba || !d_chain || !d_scratch) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    if (misaligned(d_rgba, d_chain, d_scratch, nullptr)) return fail(ROSY_TEX_ERR_ARG, "device pointers must be 16-byte aligned");
     return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba), static_cast<uint8_t*>(d_chain),
                             d_scratch, nullptr, static_cast<cudaStream_t>(stream), true, false);
 }
@@ -690,6 +695,7 @@ int rosy_tex_blocks_device(const rosy_tex_desc* desc, const void* d_rgba, const 
     int rc = device_common(desc, r);
     if (rc) return rc;
     if (!d_rgba || !d_chain || !d_blocks) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    if (misaligned(d_rgba, d_chain, d_blocks, nullptr)) return fail(ROSY_TEX_ERR_ARG, "device pointers must be 16-byte aligned");
     return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba),
                             const_cast<uint8_t*>(static_cast<const uint8_t*>(d_chain)), nullptr,
                             static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), false, true);
@@ -701,8 +707,48 @@ int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* 
     int rc = device_common(desc, r);
     if (rc) return rc;
     if (!d_rgba || !d_chain || !d_scratch || !d_blocks) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    if (misaligned(d_rgba, d_chain, d_scratch, d_blocks)) return fail(ROSY_TEX_ERR_ARG, "device pointers must be 16-byte aligned");
     return encode_on_stream(make_chain(r.w, r.h), r, static_cast<const uint8_t*>(d_rgba), static_cast<uint8_t*>(d_chain),
                             d_scratch, static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), true, true);
+}
+
+size_t rosy_tex_batch_scratch_size(int count) { return count > 0 ? mips_batch_desc_bytes(count) : 0; }
+
+int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
+                                 int do_mips, int do_blocks) {
+    if (!items || count <= 0) return fail(ROSY_TEX_ERR_ARG, "empty batch");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::vector<Resolved> rs((size_t)count);
+    std::vector<MipBatchItem> mi((size_t)count);
+    for (int i = 0; i < count; i++) {
+        int rc = device_common(&items[i].desc, rs[i]);
+        if (rc) return rc;
+        const rosy_tex_batch_item& it = items[i];
+        if (!it.d_rgba || !it.d_chain || (do_mips && !it.d_scratch) || (do_blocks && !it.d_blocks))
+            return fail(ROSY_TEX_ERR_ARG, "null device pointer in batch item");
+        if (misaligned(it.d_rgba, it.d_chain, it.d_scratch, it.d_blocks))
+            return fail(ROSY_TEX_ERR_ARG, "device pointers must be 16-byte aligned");
+        mi[i].chain = make_chain(rs[i].w, rs[i].h);
+        mi[i].normal_map = rs[i].normal_map;
+        mi[i].normalize = rs[i].normalize;
+        mi[i].d_rgba = static_cast<const uint8_t*>(it.d_rgba);
+        mi[i].d_chain = static_cast<uint8_t*>(it.d_chain);
+        mi[i].d_scratch = it.d_scratch;
+    }
+    if (do_mips) {
+        if (!d_batch_scratch) return fail(ROSY_TEX_ERR_ARG, "null batch scratch");
+        const int n = launch_mips_batch(count, mi.data(), d_batch_scratch, s);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "batched mip kernels");
+        g_launches += (uint64_t)n;
+    }
+    if (do_blocks) {
+        for (int i = 0; i < count; i++) {
+            int rc = encode_on_stream(mi[i].chain, rs[i], mi[i].d_rgba, mi[i].d_chain, nullptr,
+                                      static_cast<uint8_t*>(items[i].d_blocks), s, false, true);
+            if (rc) return rc;
+        }
+    }
+    return ROSY_TEX_OK;
 }
 
 uint64_t rosy_tex_kernel_launches(void) { return g_launches.load(); }

@@ -42,6 +42,17 @@ Bc7Tier bc7_tier(int quality);
 int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
                 uint8_t* d_chain, void* d_scratch, cudaStream_t s);
 size_t mips_scratch_bytes(const Chain& c);
+// several textures, one fused launch per image kind (ragged extents fall back to per-level launches)
+struct MipBatchItem {
+    Chain chain;
+    bool normal_map;
+    int normalize;
+    const uint8_t* d_rgba;
+    uint8_t* d_chain;
+    void* d_scratch;  // mips_scratch_bytes(chain), first 256 bytes zero
+};
+size_t mips_batch_desc_bytes(int n);
+int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream_t s);
 // bc45_encode.cu
 int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
                 const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);

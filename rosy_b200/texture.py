@@ -39,6 +39,16 @@ class Desc(C.Structure):
     ]
 
 
+class BatchItem(C.Structure):
+    _fields_ = [
+        ("desc", Desc),
+        ("d_rgba", C.c_void_p),
+        ("d_chain", C.c_void_p),
+        ("d_scratch", C.c_void_p),
+        ("d_blocks", C.c_void_p),
+    ]
+
+
 class Config(C.Structure):
     _fields_ = [
         ("struct_size", C.c_uint32),
@@ -89,6 +99,9 @@ def lib():
         L.rosy_tex_mips_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 4
         L.rosy_tex_blocks_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 4
         L.rosy_tex_encode_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 5
+        L.rosy_tex_batch_scratch_size.restype = C.c_size_t
+        L.rosy_tex_batch_scratch_size.argtypes = [C.c_int]
+        L.rosy_tex_encode_batch_device.argtypes = [C.POINTER(BatchItem), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.rosy_tex_load_image.argtypes = [C.c_char_p, C.POINTER(u8p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.rosy_tex_free_image.argtypes = [u8p]
         L.rosy_tex_generate_texture_file.argtypes = [C.c_char_p, C.c_int, C.c_char_p]
@@ -270,6 +283,22 @@ def blocks_device(d, rgba_ptr, chain_ptr, blocks_ptr, stream=0):
 
 def encode_device(d, rgba_ptr, chain_ptr, scratch_ptr, blocks_ptr, stream=0):
     _check(lib().rosy_tex_encode_device(C.byref(d), rgba_ptr, chain_ptr, scratch_ptr, blocks_ptr, stream))
+
+
+def batch_scratch_size(count):
+    return lib().rosy_tex_batch_scratch_size(int(count))
+
+
+def make_batch(entries):
+    """entries: (Desc, rgba_ptr, chain_ptr, scratch_ptr, blocks_ptr) per texture -> ctypes array"""
+    arr = (BatchItem * len(entries))()
+    for it, (d, a, b, c, e) in zip(arr, entries):
+        it.desc, it.d_rgba, it.d_chain, it.d_scratch, it.d_blocks = d, a, b, c, e
+    return arr
+
+
+def encode_batch_device(batch, batch_scratch_ptr, stream=0, do_mips=True, do_blocks=True):
+    _check(lib().rosy_tex_encode_batch_device(batch, len(batch), batch_scratch_ptr, stream, int(do_mips), int(do_blocks)))
 
 
 def kernel_launches():

@@ -2,7 +2,7 @@
 into profiles/bench_counts.json: per-launch warp-instruction and DRAM-byte counts that bench.py
 combines with its live CUDA-event durations (roofline.achieved for the issue-bound BC7 kernel).
 
-    python tools/profile_counts.py gpurun_out/r1a_launches.csv albedo-2048-bc7-normal
+    python tools/profile_counts.py gpurun_out/r1a_launches.csv albedo-2048-bc7-normal [textures per mip launch]
 """
 import collections
 import csv
@@ -13,6 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 path, key = sys.argv[1], sys.argv[2]
+tex_per_mip_launch = int(sys.argv[3]) if len(sys.argv) > 3 else 1  # textures covered by one mip launch in the profiled command
 rows = list(csv.reader(open(path)))
 hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
 hdr = rows[hi]
@@ -44,6 +45,8 @@ doc[key] = {
     "mip_warp_inst_per_launch": mean("mip", "smsp__inst_executed.sum"),
     "mip_dram_bytes_per_launch": (mean("mip", "dram__bytes_read.sum") or 0) + (mean("mip", "dram__bytes_write.sum") or 0),
     "mip_ns_per_launch_under_ncu": mean("mip", "gpu__time_duration.sum"),
+    "mip_textures_per_launch": tex_per_mip_launch,
+    "mip_dram_bytes_per_texture": ((mean("mip", "dram__bytes_read.sum") or 0) + (mean("mip", "dram__bytes_write.sum") or 0)) / tex_per_mip_launch,
 }
 json.dump(doc, open(out_path, "w"), indent=1)
 print(json.dumps(doc[key], indent=1))
