@@ -1,19 +1,22 @@
 #!/bin/bash
-# One gpurun call: bench (both arms), then the ncu launch list and --set full captures of the
-# two hot kernels on a short version of the same command (B200_PROFILING.md recipe).
+# One gpurun call: the ncu launch list first (its per-launch instruction counts feed bench.py's
+# issue-slot roofline, keyed by the kernel source hash), then bench (both arms), then --set full
+# captures of the two hot kernels on a short version of the same command (B200_PROFILING.md recipe).
 set -u
 TAG=${1:-r1}
 OUT=gpurun_out
 mkdir -p $OUT
-python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"; tail -c 3000 $OUT/${TAG}_bench.json
-python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>> $OUT/${TAG}_bench.err; echo "ref rc=$?"; tail -c 600 $OUT/${TAG}_bench_ref.json
 SHORT="python bench.py --textures 8 --steps 1 --warmup 3 --no-cpu --no-e2e"
 $SHORT > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 400 --csv \
     --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu1.log 2>&1
 echo "launch list rc=$?"
+python tools/profile_counts.py $OUT/${TAG}_launches.csv albedo-2048-bc7-normal 8 > $OUT/${TAG}_counts.log 2>&1
+cp profiles/bench_counts.json $OUT/${TAG}_bench_counts.json
+python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"; tail -c 3000 $OUT/${TAG}_bench.json
+python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>> $OUT/${TAG}_bench.err; echo "ref rc=$?"; tail -c 600 $OUT/${TAG}_bench_ref.json
 ncu --set full --clock-control none --import-source on -k regex:bc7_encode -s 24 -c 2 -f -o $OUT/${TAG}_bc7 $SHORT > $OUT/${TAG}_ncu2.log 2>&1
 echo "bc7 full rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:mip_fused -s 24 -c 2 -f -o $OUT/${TAG}_mip $SHORT > $OUT/${TAG}_ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:mip_fused -s 3 -c 1 -f -o $OUT/${TAG}_mip $SHORT > $OUT/${TAG}_ncu3.log 2>&1
 echo "mip full rc=$?"
 ls -la $OUT
