@@ -179,24 +179,32 @@ normal_level0_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, siz
 // fused path: whole chain(s) in one launch, TMA-staged 64x64 tiles
 // ------------------------------------------------------------------------------------------
 constexpr int TILE = 64;
-constexpr int STAGES = 3;
+constexpr int STAGES = 2;
 constexpr int NTHREADS = 256;        // consumer threads (warps 0-7)
 constexpr int NTHREADS_TOTAL = 320;  // + auxiliary warp 8 + producer warp 9
 constexpr int L3_BUFS = 4;           // level-3 hand-over buffers between the consumers and the auxiliary warp
 constexpr int INFO_RING = 16;        // >= STAGES + L3_BUFS + 1 tile descriptors in flight
 constexpr int TAIL_QUEUE = 64;
 constexpr int TILE_BYTES = TILE * TILE * 4;
-constexpr int TAIL_SMEM_PX = 512;  // tail levels with at most this many texels are reduced in shared memory
+constexpr int TAIL_SMEM_PX = 256;  // tail levels with at most this many texels are reduced in shared memory
 
-// linear -> sRGB8 as a piecewise-linear table over the float's exponent and top 5 mantissa bits:
-// entry 0 covers [0, 2^-9) (inside the 12.92 c segment), entries 1..288 the 32 slices of each
-// octave [2^-9, 1), entry 289 is c >= 1.  y = slope * c + intercept approximates
-// 255 * toSrgb(c) + 0.5 to better than 0.005 LSB (checked on the host when the table is built).
+// Colour values travel through the fused kernel BIASED: a working value is c' = c + SRGB_BIAS
+// (premultiplied: P' = P + SRGB_BIAS * A), which every box average preserves because its weights
+// sum to one.  The bias comes for free from the sRGB->linear table (entries hold lin/4 + bias/4) and
+// keeps every opaque value inside [2^-9, 1 + 2^-9], so the encode table below needs no clamps.
+//
+// linear -> sRGB8 as a piecewise-linear table over the float's exponent and top 5 mantissa bits of
+// c': entry e covers the slice that starts at bits SRGB_LO + (e << SRGB_SHIFT); entries 0..287 are
+// the 32 slices of each octave of [2^-9, 1), entry 288 is [1, 1 + 2^-5) (only [1, 1 + 2^-9] occurs).
+// y = slope * c' + intercept approximates 255 * toSrgb(c' - bias) + 0.5 to better than 0.01 LSB
+// (checked on the host when the table is built).
 constexpr int SRGB_SHIFT = 18;
 constexpr uint32_t SRGB_LO = 0x3B000000u;  // 2^-9
 constexpr uint32_t SRGB_HI = 0x3F800000u;  // 1.0
-constexpr int SRGB_BASE = (int)(SRGB_LO >> SRGB_SHIFT) - 1;
-constexpr int SRGB_ENTRIES = (int)((SRGB_HI - SRGB_LO) >> SRGB_SHIFT) + 2;
+constexpr float SRGB_BIAS = 0.001953125f;  // 2^-9
+constexpr float SRGB_MAX = 1.001953125f;   // 1 + 2^-9
+constexpr int SRGB_BASE = (int)(SRGB_LO >> SRGB_SHIFT);
+constexpr int SRGB_ENTRIES = (int)((SRGB_HI - SRGB_LO) >> SRGB_SHIFT) + 1;
 
 __constant__ float2 c_SRGB_ENCODE[SRGB_ENTRIES];
 __constant__ float c_UNORM8[256];  // i / 255.0f, as nvtt::Surface::load produces it
@@ -230,6 +238,7 @@ struct TileInfo {
     int tex;
     int normalize;
     uint32_t off[8];  // pixel offset of levels 0..6 in the chain buffer (fits 32 bits up to 32768^2)
+    uint32_t org[4];  // pixel index of this tile's first texel in levels 0..3 (off[l] included)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -248,12 +257,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "{\n"
         ".reg .pred p;\n"
         "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
         "@p bra WAIT_DONE;\n"
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n"
         "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
+        "r"(parity), "r"(1000000u)  // suspend-time hint (ns): the waiter sleeps until the phase completes
         : "memory");
 }
 __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int x, int y,
@@ -264,16 +273,16 @@ __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map,
         "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
         : "memory");
 }
-__device__ __forceinline__ float lds_f32(uint32_t addr) {
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-    return v;
-}
-// channel C of texel p through the bank-replicated sRGB->linear table; lanebase = shared address
-// of this lane's copy of entry 0 (entries are 128 bytes apart)
+// The sRGB->linear table and the alpha table share one array of 256-byte rows, one row per 8-bit
+// value: floats 0..31 hold (lin(v) + SRGB_BIAS) / 4 replicated across the 32 banks (conflict-free
+// for any mix of values), floats 32..63 hold v / 255 likewise.  The byte offset of a lane's copy
+// is (v << 8) | (lane * 4): ONE PRMT takes channel C of a texel and the lane bits to that offset.
 template <int C>
-__device__ __forceinline__ float lin_lookup(uint32_t lanebase, uint32_t p) {
-    return lds_f32(lanebase + (__byte_perm(p, 0u, 0x4440 + C) << 7));
+__device__ __forceinline__ float lin_lookup(const float* lin, uint32_t lane4, uint32_t p) {
+    return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lin) + __byte_perm(p, lane4, 0x5504 + (C << 4)));
+}
+__device__ __forceinline__ float alpha_lookup(const float* lin, uint32_t lane4, uint32_t p) {
+    return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lin) + 128 + __byte_perm(p, lane4, 0x5534));
 }
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
@@ -281,26 +290,28 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
-// ---- colour: linear premultiplied fp32 -> RGBA8 --------------------------------------------
-// 255 * toSrgb(c) + 0.5 through the table, floor taken by a round-down add of 2^23: the low byte
-// of the returned word is the 8-bit value
+// ---- colour: biased linear fp32 -> RGBA8 ----------------------------------------------------
+// 255 * toSrgb(c' - bias) + 0.5 through the table, floor taken by a round-down add of 2^23: the
+// low byte of the returned word is the 8-bit value.  c' must lie in [2^-9, 1 + 2^-9].
 __device__ __forceinline__ uint32_t srgb8_bits(float c, const float2* tab /* biased by SRGB_BASE */) {
-    int b = __float_as_int(c);
-    b = max(b, (int)(SRGB_LO - (1u << SRGB_SHIFT)));
-    b = min(b, (int)SRGB_HI);
-    const float2 t = tab[b >> SRGB_SHIFT];
+    const float2 t = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(tab) +
+                                                      ((__float_as_uint(c) >> (SRGB_SHIFT - 3)) & 0x7FF8u));
     return __float_as_uint(__fadd_rd(fmaf(t.x, c, t.y), 8388608.0f));
 }
-// general: v = (linear premultiplied rgb, alpha)
+// general: v = (biased linear premultiplied rgb, alpha).  The clamps cover alpha ~ 0 (the whole
+// value vanishes) and the rounding of the approximate reciprocal.
 __device__ __forceinline__ uint32_t finish_colour(float4 v, const float2* tab) {
     const float ia = v.w > 1e-12f ? rcp_approx(v.w) : 1.0f;  // demultiplyAlpha (epsilon 1e-12)
-    const uint32_t r = srgb8_bits(v.x * ia, tab), g = srgb8_bits(v.y * ia, tab), b = srgb8_bits(v.z * ia, tab);
+    const uint32_t r = srgb8_bits(fminf(fmaxf(v.x * ia, SRGB_BIAS), SRGB_MAX), tab);
+    const uint32_t g = srgb8_bits(fminf(fmaxf(v.y * ia, SRGB_BIAS), SRGB_MAX), tab);
+    const uint32_t b = srgb8_bits(fminf(fmaxf(v.z * ia, SRGB_BIAS), SRGB_MAX), tab);
     const uint32_t a = __float_as_uint(__fadd_rd(fmaf(v.w, 255.0f, 0.5f), 8388608.0f));
     const uint32_t rg = __byte_perm(r, g, 0x0040);   // r.b0, g.b0
     const uint32_t ba = __byte_perm(b, a, 0x0040);   // b.b0, a.b0
     return __byte_perm(rg, ba, 0x5410);
 }
-// opaque: alpha is exactly 1 everywhere below this texel
+// opaque: alpha is exactly 1 everywhere below this texel, the sums are exact box means of table
+// entries and stay inside the table's range by construction
 __device__ __forceinline__ uint32_t finish_opaque(float r_, float g_, float b_, const float2* tab) {
     const uint32_t r = srgb8_bits(r_, tab), g = srgb8_bits(g_, tab), b = srgb8_bits(b_, tab);
     const uint32_t rg = __byte_perm(r, g, 0x0040);
@@ -433,11 +444,10 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
 
 struct FusedSmem {
     alignas(1024) uint8_t tiles[STAGES][TILE_BYTES];
-    float lin[256 * 32];          // sRGB -> linear / 4, one copy per bank: [value][lane]
+    float lin[256 * 64];          // [value][0..31] (sRGB -> linear + bias) / 4, [value][32..63] value / 255, per bank
     float4 tailA[TAIL_SMEM_PX];
     float4 tailB[TAIL_SMEM_PX];
     float2 srgb[SRGB_ENTRIES + 2];
-    float unorm[256];
     float4 l3[L3_BUFS][64];       // level-3 values of a tile (colour: fp32; normal: packed integer sums)
     TileInfo info[INFO_RING];
     uint64_t full[STAGES];        // TMA landed (1 arrive + tx bytes)
@@ -471,10 +481,12 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 
     if (!NORMAL) {
         // each warp fills its share of the values, every value replicated across the 32 banks
-        for (int v = warp; v < 256; v += NTHREADS_TOTAL / 32) S.lin[v * 32 + lane] = c_SRGB_TO_LINEAR[v] * 0.25f;
+        for (int v = warp; v < 256; v += NTHREADS_TOTAL / 32) {
+            S.lin[v * 64 + lane] = (c_SRGB_TO_LINEAR[v] + SRGB_BIAS) * 0.25f;
+            S.lin[v * 64 + 32 + lane] = c_UNORM8[v];
+        }
         for (int i = tid; i < SRGB_ENTRIES; i += NTHREADS_TOTAL) S.srgb[i] = c_SRGB_ENCODE[i];
     }
-    if (tid < 256) S.unorm[tid] = c_UNORM8[tid];
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
             mbar_init(&S.full[s], 1);
@@ -516,6 +528,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             I.normalize = T->normalize;
 #pragma unroll
             for (int l = 0; l < 7; l++) I.off[l] = (uint32_t)T->lpx[l];
+#pragma unroll
+            for (int l = 0; l < 4; l++)
+                I.org[l] = (uint32_t)T->lpx[l] + (uint32_t)(tile_y * (TILE >> l)) * (T->w >> l) + (uint32_t)(tile_x * (TILE >> l));
             mbar_expect_tx(&S.full[s], TILE_BYTES);
             tma_load_tile(S.tiles[s], &T->tmap, tile_x * TILE, tile_y * TILE, &S.full[s]);
         }
@@ -628,7 +643,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     // ================================ consumers ================================
     const int tx = tid & 15, ty = tid >> 4;
     const bool l3_owner = ((tx | ty) & 1) == 0;
-    const uint32_t lb = smem_u32(S.lin + lane);
+    const uint32_t lane4 = (uint32_t)lane * 4u;
+    const float* lin = S.lin;
     for (int it = 0; it < my_tiles; it++) {
         const int s = it % STAGES;
         mbar_wait(&S.full[s], (uint32_t)((it / STAGES) & 1));
@@ -639,12 +655,13 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         for (int r = 0; r < 4; r++) rows[r] = trow[(4 * ty + r) * (TILE / 4) + tx];
         const TileInfo& I = S.info[it % INFO_RING];
         uint32_t* chain32 = reinterpret_cast<uint32_t*>(I.chainbuf);
-        const int tile_x = I.tile_x, tile_y = I.tile_y, normalize = I.normalize;
-        const uint32_t w0 = I.w, w1 = w0 >> 1, w2 = w0 >> 2, w3 = w0 >> 3;
-        uint32_t* c1 = chain32 + I.off[1] + (size_t)(tile_y * 32 + 2 * ty) * w1 + tile_x * 32 + 2 * tx;
-        uint32_t* c2 = chain32 + I.off[2] + (size_t)(tile_y * 16 + ty) * w2 + tile_x * 16 + tx;
-        uint32_t* c3 = chain32 + I.off[3] + (size_t)(tile_y * 8 + (ty >> 1)) * w3 + tile_x * 8 + (tx >> 1);
-        uint4* c0 = reinterpret_cast<uint4*>(chain32 + I.off[0] + (size_t)(tile_y * TILE + 4 * ty) * w0 + tile_x * TILE) + tx;
+        const int normalize = I.normalize;
+        const uint32_t w0 = I.w, w1 = w0 >> 1;
+        // 32-bit texel indices: tile origin (from the producer) + this thread's patch
+        uint32_t* c1 = chain32 + (I.org[1] + (uint32_t)(2 * ty) * w1 + 2 * tx);
+        uint32_t* c2 = chain32 + (I.org[2] + (uint32_t)ty * (w0 >> 2) + tx);
+        uint32_t* c3 = chain32 + (I.org[3] + (uint32_t)(ty >> 1) * (w0 >> 3) + (tx >> 1));
+        uint4* c0 = reinterpret_cast<uint4*>(chain32 + (I.org[0] + (uint32_t)(4 * ty) * w0 + 4 * tx));
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.empty[s]);  // the texels are in registers: the stage may be refilled
         const int b = it % L3_BUFS;
@@ -705,9 +722,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 #pragma unroll
                     for (int i = 0; i < 2; i++) {
                         const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
-                        const float r_ = (lin_lookup<0>(lb, p0) + lin_lookup<0>(lb, p1)) + (lin_lookup<0>(lb, p2) + lin_lookup<0>(lb, p3));
-                        const float g_ = (lin_lookup<1>(lb, p0) + lin_lookup<1>(lb, p1)) + (lin_lookup<1>(lb, p2) + lin_lookup<1>(lb, p3));
-                        const float b_ = (lin_lookup<2>(lb, p0) + lin_lookup<2>(lb, p1)) + (lin_lookup<2>(lb, p2) + lin_lookup<2>(lb, p3));
+                        const float r_ = (lin_lookup<0>(lin, lane4, p0) + lin_lookup<0>(lin, lane4, p1)) + (lin_lookup<0>(lin, lane4, p2) + lin_lookup<0>(lin, lane4, p3));
+                        const float g_ = (lin_lookup<1>(lin, lane4, p0) + lin_lookup<1>(lin, lane4, p1)) + (lin_lookup<1>(lin, lane4, p2) + lin_lookup<1>(lin, lane4, p3));
+                        const float b_ = (lin_lookup<2>(lin, lane4, p0) + lin_lookup<2>(lin, lane4, p1)) + (lin_lookup<2>(lin, lane4, p2) + lin_lookup<2>(lin, lane4, p3));
                         o[i] = finish_opaque(r_, g_, b_, tab);
                         sr += r_;
                         sg += g_;
@@ -729,10 +746,10 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                         float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                         for (int k = 0; k < 4; k++) {
-                            const float al = S.unorm[p[k] >> 24];
-                            q.x = fmaf(lin_lookup<0>(lb, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
-                            q.y = fmaf(lin_lookup<1>(lb, p[k]), al, q.y);
-                            q.z = fmaf(lin_lookup<2>(lb, p[k]), al, q.z);
+                            const float al = alpha_lookup(lin, lane4, p[k]);
+                            q.x = fmaf(lin_lookup<0>(lin, lane4, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
+                            q.y = fmaf(lin_lookup<1>(lin, lane4, p[k]), al, q.y);
+                            q.z = fmaf(lin_lookup<2>(lin, lane4, p[k]), al, q.z);
                             q.w += al;
                         }
                         q.w *= 0.25f;
@@ -880,20 +897,22 @@ int mips_upload_tables() {
         lut[i] = c <= 0.04045f ? c / 12.92f : powf((c + 0.055f) / 1.055f, 2.4f);
     }
     // Surface::toSrgb (row A5; NVTT-2's literal exponent 0.41666f) followed by compress()'s
-    // quantisation, y(c) = 255 s(c) + 0.5, as one line per slice of the float range
+    // quantisation, y(c') = 255 s(c' - bias) + 0.5, as one line per slice of the float range
     static float2 enc[SRGB_ENTRIES];
-    auto y = [](double c) {
+    auto y = [](double cb) {
+        const double c = cb - (double)SRGB_BIAS;
         const double s = c <= (double)0.0031308f ? (double)12.92f * c : (double)1.055f * pow(c, (double)0.41666f) - (double)0.055f;
         return 255.0 * (s < 0.0 ? 0.0 : (s > 1.0 ? 1.0 : s)) + 0.5;
     };
-    enc[0] = make_float2(12.92f * 255.0f, 0.5f);
     double worst = 0.0;
-    for (int e = 1; e < SRGB_ENTRIES - 1; e++) {
-        const uint32_t b0 = SRGB_LO + ((uint32_t)(e - 1) << SRGB_SHIFT), b1 = b0 + (1u << SRGB_SHIFT);
+    for (int e = 0; e < SRGB_ENTRIES; e++) {
+        const uint32_t b0 = SRGB_LO + ((uint32_t)e << SRGB_SHIFT), b1 = b0 + (1u << SRGB_SHIFT);
         float f0, f1;
         memcpy(&f0, &b0, 4);
         memcpy(&f1, &b1, 4);
-        const double c0 = f0, c1 = f1, slope = (y(c1) - y(c0)) / (c1 - c0);
+        // the last slice starts at 1.0 and is only ever used up to 1 + bias
+        const double c0 = f0, c1 = e == SRGB_ENTRIES - 1 ? (double)SRGB_MAX : (double)f1;
+        const double slope = (y(c1) - y(c0)) / (c1 - c0);
         double lo = 0.0, hi = 0.0;  // deviation of y from the chord
         for (int k = 0; k <= 64; k++) {
             const double c = c0 + (c1 - c0) * k / 64.0, d = y(c) - (y(c0) + slope * (c - c0));
@@ -904,7 +923,6 @@ int mips_upload_tables() {
         enc[e] = make_float2((float)slope, (float)(y(c0) - slope * c0 + shift));
         worst = fmax(worst, 0.5 * (hi - lo));
     }
-    enc[SRGB_ENTRIES - 1] = make_float2(0.0f, 255.5f);
     if (worst > 0.01) return -1;  // table must stay far inside the 1 LSB bar
     return cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
                    cudaMemcpyToSymbol(c_UNORM8, unorm, sizeof unorm) == cudaSuccess &&
