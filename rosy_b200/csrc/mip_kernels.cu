@@ -179,9 +179,11 @@ normal_level0_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, siz
 // fused path: whole chain(s) in one launch, TMA-staged 64x64 tiles
 // ------------------------------------------------------------------------------------------
 constexpr int TILE = 64;
-constexpr int STAGES = 2;
+constexpr int STAGES = 3;
 constexpr int NTHREADS = 256;        // consumer threads (warps 0-7)
-constexpr int NTHREADS_TOTAL = 320;  // + auxiliary warp 8 + producer warp 9
+constexpr int NTHREADS_TOTAL = 320;  // + auxiliary warp 8 + producer warp 9 = one group
+constexpr int GROUPS = 2;            // independent groups per CTA (one CTA per SM); they share only the tables
+constexpr int LIN_BYTES = 256 * 256; // the value tables: 64 KB at a 64 KB boundary of the shared window
 constexpr int L3_BUFS = 4;           // level-3 hand-over buffers between the consumers and the auxiliary warp
 constexpr int INFO_RING = 16;        // >= STAGES + L3_BUFS + 1 tile descriptors in flight
 constexpr int TAIL_QUEUE = 64;
@@ -277,12 +279,19 @@ __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map,
 // value: floats 0..31 hold (lin(v) + SRGB_BIAS) / 4 replicated across the 32 banks (conflict-free
 // for any mix of values), floats 32..63 hold v / 255 likewise.  The byte offset of a lane's copy
 // is (v << 8) | (lane * 4): ONE PRMT takes channel C of a texel and the lane bits to that offset.
-template <int C>
-__device__ __forceinline__ float lin_lookup(const float* lin, uint32_t lane4, uint32_t p) {
-    return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lin) + __byte_perm(p, lane4, 0x5504 + (C << 4)));
+// lanebase = shared-window address of the tables (a multiple of 64 KB) | lane * 4: the PRMT also
+// carries the two upper address bytes, so the lookup is PRMT + LDS.
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
 }
-__device__ __forceinline__ float alpha_lookup(const float* lin, uint32_t lane4, uint32_t p) {
-    return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lin) + 128 + __byte_perm(p, lane4, 0x5534));
+template <int C>
+__device__ __forceinline__ float lin_lookup(uint32_t lanebase, uint32_t p) {
+    return lds_f32(__byte_perm(p, lanebase, 0x7604 + (C << 4)));
+}
+__device__ __forceinline__ float alpha_lookup(uint32_t lanebase, uint32_t p) {
+    return lds_f32(__byte_perm(p, lanebase, 0x7634) + 128u);
 }
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
@@ -369,11 +378,11 @@ __device__ __forceinline__ uint32_t finish_any(float4 v, int normalize, const fl
 // Run by the 256 consumer threads (named barrier 1) or, if the request queue overflowed, by the
 // auxiliary warp alone (NT = 32, __syncwarp).
 template <int NT>
-__device__ __forceinline__ void tail_sync() {
+__device__ __forceinline__ void tail_sync(int bar_id) {
     if (NT == 32)
         __syncwarp();
     else
-        asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(NT) : "memory");
 }
 
 template <bool NORMAL, int NT, bool GSRC, bool GDST>
@@ -402,7 +411,7 @@ __device__ __forceinline__ void tail_level(const float4* src, int sw, int sh, fl
 }
 
 template <bool NORMAL, int NT>
-__device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, const float2* tab, int tid) {
+__device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, const float2* tab, int tid, int bar_id) {
     __threadfence();  // acquire side of the ticket: other CTAs' tile_top stores are visible
     const int levels = T->levels, normalize = T->normalize;
     uint32_t* chain32 = reinterpret_cast<uint32_t*>(T->chainbuf);
@@ -414,7 +423,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     for (; l < levels && (int)(T->lw[l] * T->lh[l]) > TAIL_SMEM_PX; l++) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
         tail_level<NORMAL, NT, true, true>(gsrc, sw, sh, gdst, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
-        tail_sync<NT>();
+        tail_sync<NT>(bar_id);
         gsrc = gdst;
         gdst = (gdst == T->tail_a) ? T->tail_b : T->tail_a;
         sw = ow;
@@ -423,7 +432,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     if (l < levels) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
         tail_level<NORMAL, NT, true, false>(gsrc, sw, sh, sA, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
-        tail_sync<NT>();
+        tail_sync<NT>(bar_id);
         sw = ow;
         sh = oh;
         l++;
@@ -432,7 +441,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     for (; l < levels; l++) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
         tail_level<NORMAL, NT, false, false>(s, sw, sh, d, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
-        tail_sync<NT>();
+        tail_sync<NT>(bar_id);
         float4* t = s;
         s = d;
         d = t;
@@ -442,12 +451,14 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     if (tid == 0) *T->ticket = 0u;  // ready for the next launch
 }
 
-struct FusedSmem {
+// Shared memory of one CTA (one per SM):
+//   [window base .. 64 KB boundary)   GroupSmem of group 0
+//   [64 KB .. 128 KB)                 value tables, 256-byte rows (see lin_lookup)
+//   [128 KB ..)                       GroupSmem of group 1, then the sRGB encode table
+struct GroupSmem {
     alignas(1024) uint8_t tiles[STAGES][TILE_BYTES];
-    float lin[256 * 64];          // [value][0..31] (sRGB -> linear + bias) / 4, [value][32..63] value / 255, per bank
     float4 tailA[TAIL_SMEM_PX];
     float4 tailB[TAIL_SMEM_PX];
-    float2 srgb[SRGB_ENTRIES + 2];
     float4 l3[L3_BUFS][64];       // level-3 values of a tile (colour: fp32; normal: packed integer sums)
     TileInfo info[INFO_RING];
     uint64_t full[STAGES];        // TMA landed (1 arrive + tx bytes)
@@ -455,37 +466,51 @@ struct FusedSmem {
     uint64_t l3full[L3_BUFS];     // every consumer warp has written its level-3 texels (8 arrives)
     uint64_t l3empty[L3_BUFS];    // the auxiliary warp has read them (1 arrive)
     uint64_t aux_done;            // the auxiliary warp has finished its last tile (1 arrive)
-    int queue[TAIL_QUEUE];        // textures whose last tile this CTA finished
+    int queue[TAIL_QUEUE];        // textures whose last tile this group finished
     int nqueue;
 };
+constexpr uint32_t SMEM_WINDOW_BASE = 0x400;  // dynamic shared memory starts 1 KB into the CTA's window (checked in the kernel)
+constexpr size_t SRGB_TAB_BYTES = (SRGB_ENTRIES + 2) * sizeof(float2);
+constexpr size_t FUSED_SMEM_BYTES = (0x10000 - SMEM_WINDOW_BASE) + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES;
+static_assert(sizeof(GroupSmem) <= 0x10000 - SMEM_WINDOW_BASE, "group 0 must fit below the 64 KB boundary");
+static_assert(FUSED_SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// Warp roles (no CTA-wide barrier anywhere in the tile loop):
+// Two independent groups of 10 warps per CTA; roles inside a group (no CTA-wide barrier anywhere in
+// the tile loop):
 //   warps 0-7  consumers: a 4x4 texel patch per thread -> levels 0 (normal maps), 1, 2, 3
 //   warp  8    auxiliary: levels 4-6 of each tile from the level-3 values, per-tile level-6 value,
 //              completion tickets; textures whose last tile it saw are queued for the tail
 //   warp  9    producer: one lane issues the TMA loads, STAGES tiles ahead
 // After the loop the consumers reduce the queued textures' level-6 images down to 1x1.
 template <bool NORMAL>
-__global__ void __launch_bounds__(NTHREADS_TOTAL, 2)
+__global__ void __launch_bounds__(NTHREADS_TOTAL * GROUPS, 1)
 mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict__ texs,
                  const int* __restrict__ tile_base, int ntex, int total_tiles) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    FusedSmem& S = *reinterpret_cast<FusedSmem*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const float2* tab = S.srgb - SRGB_BASE;
-    const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int grp = threadIdx.x >= NTHREADS_TOTAL ? 1 : 0;
+    const int tid = (int)threadIdx.x - grp * NTHREADS_TOTAL, lane = tid & 31, warp = tid >> 5;
+    const uint32_t win = smem_u32(smem_raw);
+    if ((win & 0xFFFFu) != SMEM_WINDOW_BASE) __trap();  // the layout below relies on it
+    uint8_t* const lin_raw = smem_raw + (0x10000 - SMEM_WINDOW_BASE);
+    GroupSmem& S = *reinterpret_cast<GroupSmem*>(grp ? lin_raw + LIN_BYTES : smem_raw);
+    float* const lin_tab = reinterpret_cast<float*>(lin_raw);
+    float2* const srgb_tab = reinterpret_cast<float2*>(lin_raw + LIN_BYTES + sizeof(GroupSmem));
+    const float2* tab = srgb_tab - SRGB_BASE;
+    const int vblock = (int)blockIdx.x * GROUPS + grp, vgrid = (int)gridDim.x * GROUPS;
+    const int my_tiles = (total_tiles - vblock + vgrid - 1) / vgrid;
+    const int tail_bar = 1 + grp;
 
     if (!NORMAL) {
         // each warp fills its share of the values, every value replicated across the 32 banks
-        for (int v = warp; v < 256; v += NTHREADS_TOTAL / 32) {
-            S.lin[v * 64 + lane] = (c_SRGB_TO_LINEAR[v] + SRGB_BIAS) * 0.25f;
-            S.lin[v * 64 + 32 + lane] = c_UNORM8[v];
+        for (int v = (int)(threadIdx.x >> 5); v < 256; v += NTHREADS_TOTAL * GROUPS / 32) {
+            lin_tab[v * 64 + lane] = (c_SRGB_TO_LINEAR[v] + SRGB_BIAS) * 0.25f;
+            lin_tab[v * 64 + 32 + lane] = c_UNORM8[v];
         }
-        for (int i = tid; i < SRGB_ENTRIES; i += NTHREADS_TOTAL) S.srgb[i] = c_SRGB_ENCODE[i];
+        for (int i = threadIdx.x; i < SRGB_ENTRIES; i += NTHREADS_TOTAL * GROUPS) srgb_tab[i] = c_SRGB_ENCODE[i];
     }
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
@@ -507,7 +532,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         if (lane != 0) return;
         int cur = 0;  // texture cursor: tiles are visited in increasing order
         for (int it = 0; it < my_tiles; it++) {
-            const int t = (int)blockIdx.x + it * (int)gridDim.x;
+            const int t = vblock + it * vgrid;
             const int s = it % STAGES;
             if (it >= STAGES) mbar_wait(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
             const MipTex* T = &single;
@@ -615,7 +640,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             }
             overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
             if (overflow_tex >= 0)
-                run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane);
+                run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane, 0);
             if (lane == 0) {
                 chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = finish_any<NORMAL>(v6, I.normalize, tab);
                 if (has_tail) __stcg(I.tile_top, v6);
@@ -634,7 +659,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         }
         overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
         if (overflow_tex >= 0)
-            run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane);
+            run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane, 0);
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.aux_done);
         return;
@@ -643,8 +668,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     // ================================ consumers ================================
     const int tx = tid & 15, ty = tid >> 4;
     const bool l3_owner = ((tx | ty) & 1) == 0;
-    const uint32_t lane4 = (uint32_t)lane * 4u;
-    const float* lin = S.lin;
+    const uint32_t lanebase = (win + (0x10000 - SMEM_WINDOW_BASE)) | ((uint32_t)lane * 4u);
     for (int it = 0; it < my_tiles; it++) {
         const int s = it % STAGES;
         mbar_wait(&S.full[s], (uint32_t)((it / STAGES) & 1));
@@ -722,9 +746,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 #pragma unroll
                     for (int i = 0; i < 2; i++) {
                         const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
-                        const float r_ = (lin_lookup<0>(lin, lane4, p0) + lin_lookup<0>(lin, lane4, p1)) + (lin_lookup<0>(lin, lane4, p2) + lin_lookup<0>(lin, lane4, p3));
-                        const float g_ = (lin_lookup<1>(lin, lane4, p0) + lin_lookup<1>(lin, lane4, p1)) + (lin_lookup<1>(lin, lane4, p2) + lin_lookup<1>(lin, lane4, p3));
-                        const float b_ = (lin_lookup<2>(lin, lane4, p0) + lin_lookup<2>(lin, lane4, p1)) + (lin_lookup<2>(lin, lane4, p2) + lin_lookup<2>(lin, lane4, p3));
+                        const float r_ = (lin_lookup<0>(lanebase, p0) + lin_lookup<0>(lanebase, p1)) + (lin_lookup<0>(lanebase, p2) + lin_lookup<0>(lanebase, p3));
+                        const float g_ = (lin_lookup<1>(lanebase, p0) + lin_lookup<1>(lanebase, p1)) + (lin_lookup<1>(lanebase, p2) + lin_lookup<1>(lanebase, p3));
+                        const float b_ = (lin_lookup<2>(lanebase, p0) + lin_lookup<2>(lanebase, p1)) + (lin_lookup<2>(lanebase, p2) + lin_lookup<2>(lanebase, p3));
                         o[i] = finish_opaque(r_, g_, b_, tab);
                         sr += r_;
                         sg += g_;
@@ -746,10 +770,10 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                         float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                         for (int k = 0; k < 4; k++) {
-                            const float al = alpha_lookup(lin, lane4, p[k]);
-                            q.x = fmaf(lin_lookup<0>(lin, lane4, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
-                            q.y = fmaf(lin_lookup<1>(lin, lane4, p[k]), al, q.y);
-                            q.z = fmaf(lin_lookup<2>(lin, lane4, p[k]), al, q.z);
+                            const float al = alpha_lookup(lanebase, p[k]);
+                            q.x = fmaf(lin_lookup<0>(lanebase, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
+                            q.y = fmaf(lin_lookup<1>(lanebase, p[k]), al, q.y);
+                            q.z = fmaf(lin_lookup<2>(lanebase, p[k]), al, q.z);
                             q.w += al;
                         }
                         q.w *= 0.25f;
@@ -785,8 +809,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     mbar_wait(&S.aux_done, 0u);
     const int nq = S.nqueue;
     for (int k = 0; k < nq; k++) {
-        run_tail<NORMAL, 256>(texs ? texs + S.queue[k] : &single, S.tailA, S.tailB, tab, tid);
-        tail_sync<256>();
+        run_tail<NORMAL, 256>(texs ? texs + S.queue[k] : &single, S.tailA, S.tailB, tab, tid, tail_bar);
+        tail_sync<256>(tail_bar);
     }
 }
 
@@ -864,13 +888,14 @@ cudaError_t launch_fused(const MipTex* single, const MipTex* d_texs, const int* 
     static std::once_flag once;
     std::call_once(once, [] {
         cudaFuncSetAttribute(mip_fused_kernel<NORMAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)sizeof(FusedSmem));
+                             (int)FUSED_SMEM_BYTES);
     });
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = total_tiles < 2 * sms ? total_tiles : 2 * sms;
-    mip_fused_kernel<NORMAL><<<grid, NTHREADS_TOTAL, sizeof(FusedSmem), s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
+    const int want = (total_tiles + GROUPS - 1) / GROUPS;  // every group of every CTA gets a tile
+    const int grid = want < sms ? want : sms;
+    mip_fused_kernel<NORMAL><<<grid, NTHREADS_TOTAL * GROUPS, FUSED_SMEM_BYTES, s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
     return cudaGetLastError();
 }
 
