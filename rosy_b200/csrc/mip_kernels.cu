@@ -184,11 +184,11 @@ constexpr int NTHREADS = 256;        // consumer threads (warps 0-7)
 constexpr int NTHREADS_TOTAL = 320;  // + auxiliary warp 8 + producer warp 9 = one group
 constexpr int GROUPS = 2;            // independent groups per CTA (one CTA per SM); they share only the tables
 constexpr int LIN_BYTES = 256 * 256; // the value tables: 64 KB at a 64 KB boundary of the shared window
-constexpr int L3_BUFS = 4;           // level-3 hand-over buffers between the consumers and the auxiliary warp
+constexpr int L3_BUFS = 4;           // level-2 hand-over buffers between the consumers and the auxiliary warp
 constexpr int INFO_RING = 16;        // >= STAGES + L3_BUFS + 1 tile descriptors in flight
 constexpr int TAIL_QUEUE = 64;
 constexpr int TILE_BYTES = TILE * TILE * 4;
-constexpr int TAIL_SMEM_PX = 256;  // tail levels with at most this many texels are reduced in shared memory
+constexpr int TAIL_SMEM_PX = 128;  // tail levels with at most this many texels are reduced in shared memory
 
 // Colour values travel through the fused kernel BIASED: a working value is c' = c + SRGB_BIAS
 // (premultiplied: P' = P + SRGB_BIAS * A), which every box average preserves because its weights
@@ -254,7 +254,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
                  "r"(bytes)
                  : "memory");
 }
+// Latency-critical waits (consumers, auxiliary warp): plain try_wait loop, the waiter is back the
+// moment the phase completes.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// Waits with slack (producer three tiles ahead, consumers parked until the auxiliary warp is done):
+// a suspend-time hint keeps the waiter out of the issue slots.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -264,7 +281,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n"
         "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity), "r"(1000000u)  // suspend-time hint (ns): the waiter sleeps until the phase completes
+        "r"(parity), "r"(20000u)  // suspend-time hint, ns
         : "memory");
 }
 __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int x, int y,
@@ -300,12 +317,15 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 
 // ---- colour: biased linear fp32 -> RGBA8 ----------------------------------------------------
-// 255 * toSrgb(c' - bias) + 0.5 through the table, floor taken by a round-down add of 2^23: the
-// low byte of the returned word is the 8-bit value.  c' must lie in [2^-9, 1 + 2^-9].
+// 255 * toSrgb(c' - bias) + 0.5 through the table.  The table's intercepts carry + 2^15, so the
+// FFMA result lies in [2^15, 2^15 + 256) where one ulp is 1/256: BYTE 1 of the returned word is
+// the floored 8-bit value (no separate rounding step; the packing PRMTs pick byte 1).
+// c' must lie in [2^-9, 1 + 2^-9].
+constexpr float Q8_MAGIC = 32768.0f;
 __device__ __forceinline__ uint32_t srgb8_bits(float c, const float2* tab /* biased by SRGB_BASE */) {
     const float2 t = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(tab) +
                                                       ((__float_as_uint(c) >> (SRGB_SHIFT - 3)) & 0x7FF8u));
-    return __float_as_uint(__fadd_rd(fmaf(t.x, c, t.y), 8388608.0f));
+    return __float_as_uint(fmaf(t.x, c, t.y));
 }
 // general: v = (biased linear premultiplied rgb, alpha).  The clamps cover alpha ~ 0 (the whole
 // value vanishes) and the rounding of the approximate reciprocal.
@@ -314,17 +334,27 @@ __device__ __forceinline__ uint32_t finish_colour(float4 v, const float2* tab) {
     const uint32_t r = srgb8_bits(fminf(fmaxf(v.x * ia, SRGB_BIAS), SRGB_MAX), tab);
     const uint32_t g = srgb8_bits(fminf(fmaxf(v.y * ia, SRGB_BIAS), SRGB_MAX), tab);
     const uint32_t b = srgb8_bits(fminf(fmaxf(v.z * ia, SRGB_BIAS), SRGB_MAX), tab);
-    const uint32_t a = __float_as_uint(__fadd_rd(fmaf(v.w, 255.0f, 0.5f), 8388608.0f));
-    const uint32_t rg = __byte_perm(r, g, 0x0040);   // r.b0, g.b0
-    const uint32_t ba = __byte_perm(b, a, 0x0040);   // b.b0, a.b0
+    const uint32_t a = __float_as_uint(fmaf(v.w, 255.0f, 0.5f + Q8_MAGIC));
+    const uint32_t rg = __byte_perm(r, g, 0x0051);   // r.b1, g.b1
+    const uint32_t ba = __byte_perm(b, a, 0x0051);   // b.b1, a.b1
     return __byte_perm(rg, ba, 0x5410);
 }
 // opaque: alpha is exactly 1 everywhere below this texel, the sums are exact box means of table
 // entries and stay inside the table's range by construction
 __device__ __forceinline__ uint32_t finish_opaque(float r_, float g_, float b_, const float2* tab) {
     const uint32_t r = srgb8_bits(r_, tab), g = srgb8_bits(g_, tab), b = srgb8_bits(b_, tab);
-    const uint32_t rg = __byte_perm(r, g, 0x0040);
-    return __byte_perm(rg, b, 0x0410) | 0xFF000000u;
+    const uint32_t rg = __byte_perm(r, g, 0x0051);
+    return __byte_perm(rg, b | 0x00FF0000u, 0x6510);  // r, g, b.b1, 0xFF
+}
+// packed fp32 pair add (FADD2)
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    unsigned long long ra, rb, rd;
+    float2 d;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
 }
 
 // ---- normal maps ---------------------------------------------------------------------------
@@ -454,24 +484,24 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
 // Shared memory of one CTA (one per SM):
 //   [window base .. 64 KB boundary)   GroupSmem of group 0
 //   [64 KB .. 128 KB)                 value tables, 256-byte rows (see lin_lookup)
-//   [128 KB ..)                       GroupSmem of group 1, then the sRGB encode table
+//   [128 KB ..)                       GroupSmem of group 1, the sRGB encode table, the groups' tail buffers
 struct GroupSmem {
     alignas(1024) uint8_t tiles[STAGES][TILE_BYTES];
-    float4 tailA[TAIL_SMEM_PX];
-    float4 tailB[TAIL_SMEM_PX];
-    float4 l3[L3_BUFS][64];       // level-3 values of a tile (colour: fp32; normal: packed integer sums)
     TileInfo info[INFO_RING];
     uint64_t full[STAGES];        // TMA landed (1 arrive + tx bytes)
     uint64_t empty[STAGES];       // every consumer warp holds the tile's texels in registers (8 arrives)
-    uint64_t l3full[L3_BUFS];     // every consumer warp has written its level-3 texels (8 arrives)
+    uint64_t l3full[L3_BUFS];     // every consumer warp has written its level-2 texels (8 arrives)
     uint64_t l3empty[L3_BUFS];    // the auxiliary warp has read them (1 arrive)
-    uint64_t aux_done;            // the auxiliary warp has finished its last tile (1 arrive)
+    uint64_t aux_done;            // the auxiliary warps have finished their last tiles (1 arrive)
     int queue[TAIL_QUEUE];        // textures whose last tile this group finished
     int nqueue;
 };
 constexpr uint32_t SMEM_WINDOW_BASE = 0x400;  // dynamic shared memory starts 1 KB into the CTA's window (checked in the kernel)
-constexpr size_t SRGB_TAB_BYTES = (SRGB_ENTRIES + 2) * sizeof(float2);
-constexpr size_t FUSED_SMEM_BYTES = (0x10000 - SMEM_WINDOW_BASE) + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES;
+constexpr size_t SRGB_TAB_BYTES = ((SRGB_ENTRIES + 2) * sizeof(float2) + 127) / 128 * 128;
+constexpr size_t TAIL_BYTES = 2 * TAIL_SMEM_PX * sizeof(float4);  // per group, after the encode table
+constexpr size_t L2_RING_BYTES = (size_t)L3_BUFS * 256 * sizeof(float4);  // per group: level-2 values of a tile, one per consumer thread
+constexpr size_t FUSED_SMEM_BYTES =
+    (0x10000 - SMEM_WINDOW_BASE) + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES + GROUPS * (TAIL_BYTES + L2_RING_BYTES);
 static_assert(sizeof(GroupSmem) <= 0x10000 - SMEM_WINDOW_BASE, "group 0 must fit below the 64 KB boundary");
 static_assert(FUSED_SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
@@ -500,8 +530,16 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     float* const lin_tab = reinterpret_cast<float*>(lin_raw);
     float2* const srgb_tab = reinterpret_cast<float2*>(lin_raw + LIN_BYTES + sizeof(GroupSmem));
     const float2* tab = srgb_tab - SRGB_BASE;
+    float4* const tailA = reinterpret_cast<float4*>(lin_raw + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES + grp * TAIL_BYTES);
+    float4* const tailB = tailA + TAIL_SMEM_PX;
+    float4* const l2ring = reinterpret_cast<float4*>(lin_raw + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES + GROUPS * TAIL_BYTES +
+                                                     grp * L2_RING_BYTES);
     const int vblock = (int)blockIdx.x * GROUPS + grp, vgrid = (int)gridDim.x * GROUPS;
-    const int my_tiles = (total_tiles - vblock + vgrid - 1) / vgrid;
+    // every group takes one contiguous run of tiles (balanced to +-1): few texture changes per
+    // group, so few ticket updates, and neighbouring tiles share DRAM pages
+    const int tiles_lo = total_tiles / vgrid, tiles_rem = total_tiles % vgrid;
+    const int my_tiles = tiles_lo + (vblock < tiles_rem ? 1 : 0);
+    const int first_tile = vblock * tiles_lo + (vblock < tiles_rem ? vblock : tiles_rem);
     const int tail_bar = 1 + grp;
 
     if (!NORMAL) {
@@ -532,9 +570,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         if (lane != 0) return;
         int cur = 0;  // texture cursor: tiles are visited in increasing order
         for (int it = 0; it < my_tiles; it++) {
-            const int t = vblock + it * vgrid;
+            const int t = first_tile + it;
             const int s = it % STAGES;
-            if (it >= STAGES) mbar_wait(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
+            if (it >= STAGES) mbar_wait_relaxed(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
             const MipTex* T = &single;
             if (texs) {
                 while (cur + 1 < ntex && t >= tile_base[cur + 1]) cur++;
@@ -564,72 +602,100 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 
     if (warp == 8) {
         // ================================ auxiliary ================================
-        const int l16 = lane & 15;  // lanes 16..31 mirror 0..15
-        const int x4 = l16 & 3, y4 = l16 >> 2;
-        int run_tex = -1, run_cnt = 0;  // tiles finished since the last ticket update (lane 0)
+        // Levels 3-6 of every tile from the consumers' level-2 values.  All sums are formed first
+        // (xor butterflies leave every lane of a quad with the quad's sum), then every lane finishes
+        // three texels in one go: two of level 3 and one of level 4, 5 or 6 picked by its role.
+        const int X = lane & 7, Ya = lane >> 3;
+        const bool useB = (X & 1) != 0;  // rows 4..7 of level 3 (the "b" half) instead of rows 0..3
+        // role of the lane's third texel
+        const int role = (Ya & 1) == 0 ? 4 : ((Ya == 1 && (X & 3) < 2) ? 5 : ((Ya == 3 && X == 0) ? 6 : 0));
+        const int boss = 24;  // the role-6 lane also owns the tile_top store and the tickets
+        int run_tex = -1, run_cnt = 0;  // tiles finished since the last ticket update (boss lane)
         auto flush_ticket = [&]() {
-            // lane 0: publish run_cnt finished tiles of texture run_tex; queue the tail if they were the last
+            // boss: publish run_cnt finished tiles of texture run_tex; queue the tail if they were the last
             const MipTex* T = texs ? texs + run_tex : &single;
             __threadfence();  // release: this thread's tile_top stores
             const unsigned done = atomicAdd(T->ticket, (unsigned)run_cnt) + (unsigned)run_cnt;
             return done == (unsigned)(T->tiles_x * T->tiles_y);
+        };
+        auto bfly = [](float4 v, int m) {
+            v.x += __shfl_xor_sync(0xFFFFFFFFu, v.x, m);
+            v.y += __shfl_xor_sync(0xFFFFFFFFu, v.y, m);
+            v.z += __shfl_xor_sync(0xFFFFFFFFu, v.z, m);
+            v.w += __shfl_xor_sync(0xFFFFFFFFu, v.w, m);
+            return v;
         };
         for (int it = 0; it < my_tiles; it++) {
             const int b = it % L3_BUFS;
             mbar_wait(&S.l3full[b], (uint32_t)((it / L3_BUFS) & 1));
             const TileInfo I = S.info[it % INFO_RING];
             uint32_t* chain32 = reinterpret_cast<uint32_t*>(I.chainbuf);
-            const float4* l3buf = S.l3[b];
-            float4 v4;
-            uint32_t px4;
-            if (NORMAL) {
-                const uint2* q = reinterpret_cast<const uint2*>(l3buf);
-                const uint2 a = q[(2 * y4) * 8 + 2 * x4], bq = q[(2 * y4) * 8 + 2 * x4 + 1];
-                const uint2 c = q[(2 * y4 + 1) * 8 + 2 * x4], d = q[(2 * y4 + 1) * 8 + 2 * x4 + 1];
-                const uint32_t rb4 = a.x + bq.x + c.x + d.x, ga4 = a.y + bq.y + c.y + d.y;  // <= 65280 per lane
-                px4 = finish_normal_sums<4>(rb4, ga4, I.normalize);
+            const uint32_t w3 = I.w >> 3, w4 = I.w >> 4, w5 = I.w >> 5, w6 = I.w >> 6;
+            uint32_t* c3a = chain32 + (I.org[3] + (uint32_t)Ya * w3 + X);
+            uint32_t* c3b = c3a + 4 * w3;
+            uint32_t px3a, px3b, pxc;
+            float4 v6;
+            if (!NORMAL) {
+                const float4* qa = l2ring + b * 256 + (2 * Ya) * 16 + 2 * X;  // level-3 rows Ya and Ya + 4
+                const float4* qb = qa + 8 * 16;
+                const float4 va = scale4(add4(add4(qa[0], qa[1]), add4(qa[16], qa[17])), 0.25f);
+                const float4 vb = scale4(add4(add4(qb[0], qb[1]), add4(qb[16], qb[17])), 0.25f);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.l3empty[b]);  // the level-2 buffer may be overwritten
+                const float4 v4a = scale4(bfly(bfly(va, 1), 8), 0.25f);
+                const float4 v4b = scale4(bfly(bfly(vb, 1), 8), 0.25f);
+                const float4 v5a = scale4(bfly(bfly(v4a, 2), 16), 0.25f);
+                const float4 v5b = scale4(bfly(bfly(v4b, 2), 16), 0.25f);
+                v6 = scale4(bfly(add4(v5a, v5b), 4), 0.25f);
+                const float4 s4 = useB ? v4b : v4a, s5 = useB ? v5b : v5a;
+                const float4 vc = role == 4 ? s4 : (role == 5 ? s5 : v6);
+                px3a = finish_colour(va, tab);
+                px3b = finish_colour(vb, tab);
+                pxc = finish_colour(vc, tab);
+            } else {
+                const uint2* qa = reinterpret_cast<const uint2*>(l2ring + b * 256) + (2 * Ya) * 16 + 2 * X;
+                const uint2* qb = qa + 8 * 16;
+                const uint2 a0 = qa[0], a1 = qa[1], a2 = qa[16], a3 = qa[17];
+                const uint2 b0 = qb[0], b1 = qb[1], b2 = qb[16], b3 = qb[17];
+                const uint32_t rb3a = a0.x + a1.x + a2.x + a3.x, ga3a = a0.y + a1.y + a2.y + a3.y;
+                const uint32_t rb3b = b0.x + b1.x + b2.x + b3.x, ga3b = b0.y + b1.y + b2.y + b3.y;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.l3empty[b]);
+                auto ibfly = [](uint32_t v, int m) { return v + __shfl_xor_sync(0xFFFFFFFFu, v, m); };
+                // level 4: exact sums over 256 texels, <= 65280 per 16-bit lane
+                const uint32_t rb4a = ibfly(ibfly(rb3a, 1), 8), ga4a = ibfly(ibfly(ga3a, 1), 8);
+                const uint32_t rb4b = ibfly(ibfly(rb3b, 1), 8), ga4b = ibfly(ibfly(ga3b, 1), 8);
                 // from here on fp32 means in [0,1]: exact integers scaled once
                 const float k = 1.0f / (256.0f * 255.0f);
-                v4 = make_float4((float)(rb4 & 0xFFFFu) * k, (float)(ga4 & 0xFFFFu) * k, (float)(rb4 >> 16) * k,
-                                 (float)(ga4 >> 16) * k);
-            } else {
-                v4 = scale4(add4(add4(l3buf[(2 * y4) * 8 + 2 * x4], l3buf[(2 * y4) * 8 + 2 * x4 + 1]),
-                                 add4(l3buf[(2 * y4 + 1) * 8 + 2 * x4], l3buf[(2 * y4 + 1) * 8 + 2 * x4 + 1])),
-                            0.25f);
-                px4 = finish_colour(v4, tab);
+                const float4 v4a = make_float4((float)(rb4a & 0xFFFFu) * k, (float)(ga4a & 0xFFFFu) * k,
+                                               (float)(rb4a >> 16) * k, (float)(ga4a >> 16) * k);
+                const float4 v4b = make_float4((float)(rb4b & 0xFFFFu) * k, (float)(ga4b & 0xFFFFu) * k,
+                                               (float)(rb4b >> 16) * k, (float)(ga4b >> 16) * k);
+                const float4 v5a = scale4(bfly(bfly(v4a, 2), 16), 0.25f);
+                const float4 v5b = scale4(bfly(bfly(v4b, 2), 16), 0.25f);
+                v6 = scale4(bfly(add4(v5a, v5b), 4), 0.25f);
+                px3a = finish_normal_sums<3>(rb3a, ga3a, I.normalize);
+                px3b = finish_normal_sums<3>(rb3b, ga3b, I.normalize);
+                const uint32_t p4 = finish_normal_sums<4>(useB ? rb4b : rb4a, useB ? ga4b : ga4a, I.normalize);
+                const float4 s5 = useB ? v5b : v5a;
+                const uint32_t pf = finish_pixel<true>(role == 5 ? s5 : v6, I.normalize);
+                pxc = role == 4 ? p4 : pf;
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&S.l3empty[b]);  // the level-3 buffer may be overwritten
-            const uint32_t w4 = I.w >> 4, w5 = I.w >> 5, w6 = I.w >> 6;
-            if (lane < 16) chain32[I.off[4] + (size_t)(I.tile_y * 4 + y4) * w4 + I.tile_x * 4 + x4] = px4;
-            float4 v5 = v4;
-            v5.x += __shfl_xor_sync(0xFFFFFFFFu, v5.x, 1);
-            v5.y += __shfl_xor_sync(0xFFFFFFFFu, v5.y, 1);
-            v5.z += __shfl_xor_sync(0xFFFFFFFFu, v5.z, 1);
-            v5.w += __shfl_xor_sync(0xFFFFFFFFu, v5.w, 1);
-            v5.x += __shfl_xor_sync(0xFFFFFFFFu, v5.x, 4);
-            v5.y += __shfl_xor_sync(0xFFFFFFFFu, v5.y, 4);
-            v5.z += __shfl_xor_sync(0xFFFFFFFFu, v5.z, 4);
-            v5.w += __shfl_xor_sync(0xFFFFFFFFu, v5.w, 4);
-            v5 = scale4(v5, 0.25f);
-            if (lane < 16 && ((x4 | y4) & 1) == 0)
-                chain32[I.off[5] + (size_t)(I.tile_y * 2 + (y4 >> 1)) * w5 + I.tile_x * 2 + (x4 >> 1)] =
-                    finish_any<NORMAL>(v5, I.normalize, tab);
-            float4 v6 = v5;
-            v6.x += __shfl_xor_sync(0xFFFFFFFFu, v6.x, 2);
-            v6.y += __shfl_xor_sync(0xFFFFFFFFu, v6.y, 2);
-            v6.z += __shfl_xor_sync(0xFFFFFFFFu, v6.z, 2);
-            v6.w += __shfl_xor_sync(0xFFFFFFFFu, v6.w, 2);
-            v6.x += __shfl_xor_sync(0xFFFFFFFFu, v6.x, 8);
-            v6.y += __shfl_xor_sync(0xFFFFFFFFu, v6.y, 8);
-            v6.z += __shfl_xor_sync(0xFFFFFFFFu, v6.z, 8);
-            v6.w += __shfl_xor_sync(0xFFFFFFFFu, v6.w, 8);
-            v6 = scale4(v6, 0.25f);
-            // ticket bookkeeping is warp-uniform (every lane reads the same TileInfo); lane 0 acts
             const bool has_tail = I.tile_top != nullptr;
+            *c3a = px3a;
+            *c3b = px3b;
+            if (role == 4)
+                chain32[I.off[4] + (size_t)(I.tile_y * 4 + (Ya >> 1) + (useB ? 2 : 0)) * w4 + I.tile_x * 4 + (X >> 1)] = pxc;
+            else if (role == 5)
+                chain32[I.off[5] + (size_t)(I.tile_y * 2 + (useB ? 1 : 0)) * w5 + I.tile_x * 2 + (X >> 2)] = pxc;
+            else if (role == 6) {
+                chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = pxc;
+                if (has_tail) __stcg(I.tile_top, v6);
+            }
+            // ticket bookkeeping is warp-uniform (every lane reads the same TileInfo); the boss lane acts
             int overflow_tex = -1;
             if (run_tex >= 0 && run_tex != I.tex) {
-                if (lane == 0 && flush_ticket()) {
+                if (lane == boss && flush_ticket()) {
                     if (S.nqueue < TAIL_QUEUE)
                         S.queue[S.nqueue++] = run_tex;
                     else
@@ -637,13 +703,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 }
                 run_tex = -1;
                 run_cnt = 0;
-            }
-            overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
-            if (overflow_tex >= 0)
-                run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane, 0);
-            if (lane == 0) {
-                chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = finish_any<NORMAL>(v6, I.normalize, tab);
-                if (has_tail) __stcg(I.tile_top, v6);
+                overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, boss);
+                if (overflow_tex >= 0)
+                    run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, tailA, tailB, tab, lane, 0);
             }
             if (has_tail) {
                 run_tex = I.tex;
@@ -651,15 +713,15 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             }
         }
         int overflow_tex = -1;
-        if (run_tex >= 0 && lane == 0 && flush_ticket()) {
+        if (run_tex >= 0 && lane == boss && flush_ticket()) {
             if (S.nqueue < TAIL_QUEUE)
                 S.queue[S.nqueue++] = run_tex;
             else
                 overflow_tex = run_tex;
         }
-        overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, 0);
+        overflow_tex = __shfl_sync(0xFFFFFFFFu, overflow_tex, boss);
         if (overflow_tex >= 0)
-            run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, S.tailA, S.tailB, tab, lane, 0);
+            run_tail<NORMAL, 32>(texs ? texs + overflow_tex : &single, tailA, tailB, tab, lane, 0);
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.aux_done);
         return;
@@ -667,7 +729,6 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 
     // ================================ consumers ================================
     const int tx = tid & 15, ty = tid >> 4;
-    const bool l3_owner = ((tx | ty) & 1) == 0;
     const uint32_t lanebase = (win + (0x10000 - SMEM_WINDOW_BASE)) | ((uint32_t)lane * 4u);
     for (int it = 0; it < my_tiles; it++) {
         const int s = it % STAGES;
@@ -684,12 +745,10 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         // 32-bit texel indices: tile origin (from the producer) + this thread's patch
         uint32_t* c1 = chain32 + (I.org[1] + (uint32_t)(2 * ty) * w1 + 2 * tx);
         uint32_t* c2 = chain32 + (I.org[2] + (uint32_t)ty * (w0 >> 2) + tx);
-        uint32_t* c3 = chain32 + (I.org[3] + (uint32_t)(ty >> 1) * (w0 >> 3) + (tx >> 1));
         uint4* c0 = reinterpret_cast<uint4*>(chain32 + (I.org[0] + (uint32_t)(4 * ty) * w0 + 4 * tx));
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.empty[s]);  // the texels are in registers: the stage may be refilled
         const int b = it % L3_BUFS;
-        float4* l3buf = S.l3[b];
 
         if (NORMAL) {
             // level 0 of a normal map is the re-normalised input (Packager.cpp:294-296 at mip 0)
@@ -721,16 +780,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 ga2 += ga_l + ga_r;
             }
             *c2 = finish_normal_sums<2>(rb2, ga2, normalize);
-            uint32_t rb3 = rb2, ga3 = ga2;
-            rb3 += __shfl_xor_sync(0xFFFFFFFFu, rb3, 1);
-            ga3 += __shfl_xor_sync(0xFFFFFFFFu, ga3, 1);
-            rb3 += __shfl_xor_sync(0xFFFFFFFFu, rb3, 16);
-            ga3 += __shfl_xor_sync(0xFFFFFFFFu, ga3, 16);
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
-            if (l3_owner) {
-                *c3 = finish_normal_sums<3>(rb3, ga3, normalize);
-                reinterpret_cast<uint2*>(l3buf)[(ty >> 1) * 8 + (tx >> 1)] = make_uint2(rb3, ga3);
-            }
+            reinterpret_cast<uint2*>(l2ring + b * 256)[tid] = make_uint2(rb2, ga2);
         } else {
             uint32_t all = rows[0].x & rows[0].y & rows[0].z & rows[0].w;
 #pragma unroll
@@ -738,7 +789,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             const bool opaque = __all_sync(0xFFFFFFFFu, all >= 0xFF000000u);
             float4 v2;
             if (opaque) {
-                float sr = 0.f, sg = 0.f, sb = 0.f;
+                float2 srg = make_float2(0.f, 0.f);
+                float sb = 0.f;
 #pragma unroll
                 for (int j = 0; j < 2; j++) {
                     const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
@@ -746,17 +798,18 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 #pragma unroll
                     for (int i = 0; i < 2; i++) {
                         const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
-                        const float r_ = (lin_lookup<0>(lanebase, p0) + lin_lookup<0>(lanebase, p1)) + (lin_lookup<0>(lanebase, p2) + lin_lookup<0>(lanebase, p3));
-                        const float g_ = (lin_lookup<1>(lanebase, p0) + lin_lookup<1>(lanebase, p1)) + (lin_lookup<1>(lanebase, p2) + lin_lookup<1>(lanebase, p3));
+                        const float2 rg = add2(add2(make_float2(lin_lookup<0>(lanebase, p0), lin_lookup<1>(lanebase, p0)),
+                                                    make_float2(lin_lookup<0>(lanebase, p1), lin_lookup<1>(lanebase, p1))),
+                                               add2(make_float2(lin_lookup<0>(lanebase, p2), lin_lookup<1>(lanebase, p2)),
+                                                    make_float2(lin_lookup<0>(lanebase, p3), lin_lookup<1>(lanebase, p3))));
                         const float b_ = (lin_lookup<2>(lanebase, p0) + lin_lookup<2>(lanebase, p1)) + (lin_lookup<2>(lanebase, p2) + lin_lookup<2>(lanebase, p3));
-                        o[i] = finish_opaque(r_, g_, b_, tab);
-                        sr += r_;
-                        sg += g_;
+                        o[i] = finish_opaque(rg.x, rg.y, b_, tab);
+                        srg = add2(srg, rg);
                         sb += b_;
                     }
                     *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
                 }
-                v2 = make_float4(sr * 0.25f, sg * 0.25f, sb * 0.25f, 1.0f);
+                v2 = make_float4(srg.x * 0.25f, srg.y * 0.25f, sb * 0.25f, 1.0f);
                 *c2 = finish_opaque(v2.x, v2.y, v2.z, tab);
             } else {
                 float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -785,31 +838,18 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 v2 = scale4(sum, 0.25f);
                 *c2 = finish_colour(v2, tab);
             }
-            // level 3: 2x2 threads (lane ^ 1 = tx neighbour, lane ^ 16 = ty neighbour)
-            float4 v3 = v2;
-            v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 1);
-            v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 1);
-            v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 1);
-            v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 1);
-            v3.x += __shfl_xor_sync(0xFFFFFFFFu, v3.x, 16);
-            v3.y += __shfl_xor_sync(0xFFFFFFFFu, v3.y, 16);
-            v3.z += __shfl_xor_sync(0xFFFFFFFFu, v3.z, 16);
-            v3.w += __shfl_xor_sync(0xFFFFFFFFu, v3.w, 16);
-            v3 = scale4(v3, 0.25f);
+            // levels 3.. are the auxiliary warp's: hand over this thread's level-2 value
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
-            if (l3_owner) {
-                l3buf[(ty >> 1) * 8 + (tx >> 1)] = v3;
-                *c3 = finish_colour(v3, tab);
-            }
+            l2ring[b * 256 + tid] = v2;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.l3full[b]);
     }
     // ---- tails of the textures whose last tile was finished by this CTA ----
-    mbar_wait(&S.aux_done, 0u);
-    const int nq = S.nqueue;
+    mbar_wait_relaxed(&S.aux_done, 0u);
+    const int nq = S.nqueue < TAIL_QUEUE ? S.nqueue : TAIL_QUEUE;
     for (int k = 0; k < nq; k++) {
-        run_tail<NORMAL, 256>(texs ? texs + S.queue[k] : &single, S.tailA, S.tailB, tab, tid, tail_bar);
+        run_tail<NORMAL, 256>(texs ? texs + S.queue[k] : &single, tailA, tailB, tab, tid, tail_bar);
         tail_sync<256>(tail_bar);
     }
 }
@@ -945,7 +985,7 @@ int mips_upload_tables() {
             hi = d > hi ? d : hi;
         }
         const double shift = 0.5 * (lo + hi);
-        enc[e] = make_float2((float)slope, (float)(y(c0) - slope * c0 + shift));
+        enc[e] = make_float2((float)slope, (float)(y(c0) - slope * c0 + shift + (double)Q8_MAGIC));
         worst = fmax(worst, 0.5 * (hi - lo));
     }
     if (worst > 0.01) return -1;  // table must stay far inside the 1 LSB bar
