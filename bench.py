@@ -9,7 +9,7 @@ Mpix = level-0 pixels; every texture additionally carries its 11 
 
 One "step" = one pass of the hot path over the rank's batch:
   value : inputs already resident in HBM, rosy_tex_encode_batch_device() on one stream (one mip launch
-          for the step's textures, one encoder launch per texture; --per-texture: rosy_tex_mips_device /
+          and one BC7 launch for the step's textures; --per-texture: rosy_tex_mips_device /
           rosy_tex_blocks_device per texture),
           timed with CUDA events on that stream (barrier + synchronize both sides, max over ranks)
   e2e   : the same batch through the reference-facing C ABI with HOST buffers
@@ -293,7 +293,7 @@ def main():
     for i, img in enumerate(textures):
         d_in[i].copy_(torch.from_numpy(img.reshape(-1)))
     # one chain / scratch buffer per texture: the step is ONE batched call (one mip launch for the
-    # whole batch, then one encoder launch per texture)
+    # whole batch, then one BC7 launch for the whole batch)
     scratch_bytes = T.device_scratch_size(d)
     chain_pitch = (chain_bytes + 255) // 256 * 256  # device pointers must be 16-byte aligned
     d_chain = torch.empty((n, chain_pitch), dtype=torch.uint8, device=dev)
@@ -353,12 +353,14 @@ def main():
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
     value = world * mpix_step / (ms_step * 1e-3)
-    # per-launch durations: the batched step has ONE mip launch (all n textures) and n encoder launches
+    # per-launch durations: the batched step has ONE mip launch (all n textures) and ONE BC7 launch (BC4/BC5: n launches)
     used = [evs if args.per_texture else evs[:1] for evs in kernel_events]
     mip_ms = float(np.mean([ea.elapsed_time(eb) for evs in used for (ea, eb, ec) in evs]))
     enc_ms = float(np.mean([eb.elapsed_time(ec) for evs in used for (ea, eb, ec) in evs]))
     mip_tex_per_launch = 1 if args.per_texture else n
-    if not args.per_texture:
+    # the batched call encodes every BC7 texture of the step in ONE launch (BC4/BC5: one launch per texture)
+    enc_tex_per_launch = n if (not args.per_texture and fmt == T.FORMAT_BC7) else 1
+    if not args.per_texture and fmt != T.FORMAT_BC7:
         enc_ms /= n
     clk = clocks.summary()
 
@@ -424,7 +426,7 @@ def main():
     # is rewritten); encoders read 4 B/px and write 1 (BC7/BC5) or 0.5 (BC4) B/px over 4N/3 px
     chain_px = chain_bytes // 4
     mip_bytes = (4 * npx + 4 * (chain_px - npx) + (4 * npx if kind == T.KIND_NORMAL_MAP else 0)) * mip_tex_per_launch
-    enc_bytes = 4 * chain_px + blk_bytes
+    enc_bytes = (4 * chain_px + blk_bytes) * enc_tex_per_launch
     mip_gbs = mip_bytes / (mip_ms * 1e-3) / 1e9
     enc_gbs = enc_bytes / (enc_ms * 1e-3) / 1e9
     prof = load_profile_counts(args)
@@ -439,16 +441,17 @@ def main():
             "peak": issue_peak,
             "unit": "Gwarp-inst/s",
             "frac": None,
-            "traffic": prof.get("bc7_dram_bytes_per_launch"),
+            "traffic": (prof["bc7_dram_bytes_per_texture"] * enc_tex_per_launch if prof.get("bc7_dram_bytes_per_texture") else None),
             "ms_per_launch": enc_ms,
-            "share_of_step": enc_ms * n / ms_step,
+            "textures_per_launch": enc_tex_per_launch,
+            "share_of_step": enc_ms * (n // enc_tex_per_launch) / ms_step,
             "hbm": {"achieved": enc_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": enc_gbs / hbm_peak,
                     "algorithmic_bytes_per_launch": enc_bytes, "peak_source": peak_src},
             "note": "BC7 is issue-slot bound (north_star): achieved = ncu smsp__inst_executed.sum per launch "
             "(profiles/) / live CUDA-event duration; peak = 148 SMs x 4 schedulers x SM clock under load",
         }
-        if prof.get("bc7_warp_inst_per_launch"):
-            a = prof["bc7_warp_inst_per_launch"] / (enc_ms * 1e-3) / 1e9
+        if prof.get("bc7_warp_inst_per_texture"):
+            a = prof["bc7_warp_inst_per_texture"] * enc_tex_per_launch / (enc_ms * 1e-3) / 1e9
             roofline["achieved"] = a
             roofline["frac"] = a / issue_peak
             roofline["inst_source"] = prof.get("source")
@@ -456,7 +459,7 @@ def main():
         roofline = {
             "kernel": enc_kernel, "bound": "hbm", "achieved": enc_gbs, "peak": hbm_peak, "unit": "GB/s",
             "frac": enc_gbs / hbm_peak, "traffic": None, "ms_per_launch": enc_ms,
-            "share_of_step": enc_ms * n / ms_step, "algorithmic_bytes_per_launch": enc_bytes,
+            "share_of_step": enc_ms * (n // enc_tex_per_launch) / ms_step, "algorithmic_bytes_per_launch": enc_bytes,
             "peak_source": peak_src,
         }
     roofline_mip = {
@@ -530,7 +533,7 @@ def load_profile_counts(args):
         sha = hashlib.sha256(f.read()).hexdigest()[:16]
     if ent.get("bc7_source_sha") and ent["bc7_source_sha"] != sha:
         ent = dict(ent)
-        ent.pop("bc7_warp_inst_per_launch", None)  # stale: counted on another version of the kernel
+        ent.pop("bc7_warp_inst_per_texture", None)  # stale: counted on another version of the kernel
     return ent
 
 

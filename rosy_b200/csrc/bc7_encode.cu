@@ -27,13 +27,22 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+#include <vector>
+
 #include "bc7_tables.cuh"
 #include "tex_internal.h"
 
 namespace rosy_tex {
 namespace {
 
-constexpr int NT = 128;   // threads (= blocks) per CTA
+#ifndef BC7_NT
+#define BC7_NT 512
+#endif
+#ifndef BC7_JOB_SYNC
+#define BC7_JOB_SYNC 0
+#endif
+constexpr int NT = BC7_NT;   // threads (= blocks) per CTA
 constexpr int TOPK = 6;   // most partitions refined per mode (high tier)
 constexpr int MAXJOBS = 96;
 
@@ -726,13 +735,31 @@ __device__ __forceinline__ uint4 pack_solution(const Shared& S, int tid) {
 // ---- kernel ----------------------------------------------------------------------------------
 
 #ifndef BC7_MIN_CTAS
-#define BC7_MIN_CTAS 4
+#define BC7_MIN_CTAS (512 / BC7_NT)
 #endif
-__global__ void __launch_bounds__(NT, BC7_MIN_CTAS) bc7_encode_kernel(const __grid_constant__ Params P) {
-    __shared__ Shared S;
+// One texture (P1, plist == nullptr) or a batch of textures of one quality tier: plist[t] describes
+// texture t, whose blocks are threads base[t] .. base[t+1]-1 of the launch.  A CTA may straddle two
+// textures: every thread is independent.
+__global__ void __launch_bounds__(NT, BC7_MIN_CTAS)
+bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ plist,
+                  const uint64_t* __restrict__ base_of, int ntex) {
+    extern __shared__ __align__(16) uint8_t bc7_smem[];
+    Shared& S = *reinterpret_cast<Shared*>(bc7_smem);
     const int tid = threadIdx.x;
-    const uint64_t b = (uint64_t)blockIdx.x * NT + tid;
+    uint64_t b = (uint64_t)blockIdx.x * NT + tid;
+    const Params* Pp = &P1;
+    if (plist) {
+        int lo = 0, hi = ntex;  // base_of[lo] <= b < base_of[hi]  (threads past the end use the last texture)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (b >= base_of[mid]) lo = mid; else hi = mid;
+        }
+        Pp = plist + lo;
+        b -= base_of[lo];
+    }
+    const Params& P = *Pp;
     const bool live = b < P.num_blocks;
+    uint4* const outp = live ? reinterpret_cast<uint4*>(P.out) + b : nullptr;  // the only thing kept of P and b
     // which level does this block belong to?
     const uint64_t gb = P.first_block + (live ? b : 0);
     int level = P.first_level;
@@ -805,6 +832,11 @@ __global__ void __launch_bounds__(NT, BC7_MIN_CTAS) bc7_encode_kernel(const __gr
     const int njobs = c_NJOBS[tier];
 #pragma unroll 1
     for (int j = 0; j < njobs; j++) {
+#if BC7_JOB_SYNC
+        // keep the CTA's warps on the same job: the code of one job fits the instruction caches,
+        // the whole search does not (data hazards do not exist: a thread only touches its own column)
+        if ((j % BC7_JOB_SYNC) == 0) __syncthreads();
+#endif
         const uint2 jw = c_JOBS[tier][j];
         const int type = jw.x & 3, areq = (jw.y >> 4) & 3;
         const bool on = search && (areq == AREQ_ANY || (areq == AREQ_ALPHA) == has_alpha);
@@ -923,7 +955,7 @@ __global__ void __launch_bounds__(NT, BC7_MIN_CTAS) bc7_encode_kernel(const __gr
             S.best[11][tid] = (uint32_t)mode | ((uint32_t)partition << 3) | ((uint32_t)rot << 9) | ((uint32_t)idxsel << 11);
         }
     }
-    if (live) reinterpret_cast<uint4*>(P.out)[b] = pack_solution(S, tid);
+    if (outp) *outp = pack_solution(S, tid);
 }
 
 }  // namespace
@@ -1051,9 +1083,65 @@ int bc7_upload_tables() {
     return e == cudaSuccess ? 0 : -1;
 }
 
-int launch_bc7(const Chain& c, int first_level, int num_levels, int quality, const uint8_t* d_level0,
-               const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
-    Params P;
+// function attributes are per device: set once on each device that launches
+static void prepare_launch() {
+    static std::once_flag once[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::call_once(once[dev & 63], [] {
+        cudaFuncSetAttribute(bc7_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared));
+    });
+}
+
+static void fill_params(Params& P, const Chain& c, int first_level, int num_levels, int quality,
+                        const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks);
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+size_t bc7_batch_desc_bytes(int n) {
+    return align256((size_t)n * sizeof(Params)) + align256((size_t)(n + 1) * sizeof(uint64_t));
+}
+
+// BC7 blocks of n textures (all levels each): one launch per quality tier present.  d_desc:
+// bc7_batch_desc_bytes(n) bytes of device memory that must stay untouched until the launches ran.
+int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_t s) {
+    prepare_launch();
+    int launches = 0;
+    uint8_t* dd = reinterpret_cast<uint8_t*>(d_desc);
+    size_t used = 0;
+    std::vector<Params> ps;
+    std::vector<uint64_t> base;
+    for (int tier = 0; tier < 3; tier++) {
+        ps.clear();
+        base.clear();
+        uint64_t total = 0;
+        for (int i = 0; i < n; i++) {
+            const int q = items[i].quality < 0 ? 0 : (items[i].quality > 2 ? 2 : items[i].quality);
+            if (q != tier) continue;
+            Params P;
+            fill_params(P, items[i].chain, 0, items[i].chain.levels, q, items[i].d_level0, items[i].d_chain, items[i].d_blocks);
+            base.push_back(total);
+            total += P.num_blocks;
+            ps.push_back(P);
+        }
+        if (ps.empty()) continue;
+        base.push_back(total);
+        const size_t pb = align256(ps.size() * sizeof(Params)), bb = align256(base.size() * sizeof(uint64_t));
+        Params* d_ps = reinterpret_cast<Params*>(dd + used);
+        uint64_t* d_base = reinterpret_cast<uint64_t*>(dd + used + pb);
+        used += pb + bb;
+        if (cudaMemcpyAsync(d_ps, ps.data(), ps.size() * sizeof(Params), cudaMemcpyHostToDevice, s) != cudaSuccess ||
+            cudaMemcpyAsync(d_base, base.data(), base.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, s) != cudaSuccess)
+            return -1;
+        const uint64_t grid = (total + NT - 1) / NT;
+        bc7_encode_kernel<<<(unsigned)grid, NT, sizeof(Shared), s>>>(ps[0], d_ps, d_base, (int)ps.size());
+        if (cudaGetLastError() != cudaSuccess) return -1;
+        launches++;
+    }
+    return launches;
+}
+
+static void fill_params(Params& P, const Chain& c, int first_level, int num_levels, int quality,
+                        const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks) {
     P.chain = c;
     P.tier = quality < 0 ? 0 : (quality > 2 ? 2 : quality);
     P.ls_rounds = kTiers[P.tier].ls_rounds;
@@ -1066,8 +1154,15 @@ int launch_bc7(const Chain& c, int first_level, int num_levels, int quality, con
     const int last = first_level + num_levels - 1;
     P.num_blocks = c.lv[last].blk_offset + (uint64_t)c.lv[last].bw * c.lv[last].bh - P.first_block;
     P.out = d_blocks + 16ull * P.first_block;
+}
+
+int launch_bc7(const Chain& c, int first_level, int num_levels, int quality, const uint8_t* d_level0,
+               const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
+    Params P;
+    fill_params(P, c, first_level, num_levels, quality, d_level0, d_chain, d_blocks);
     const uint64_t grid = (P.num_blocks + NT - 1) / NT;
-    bc7_encode_kernel<<<(unsigned)grid, NT, 0, s>>>(P);
+    prepare_launch();
+    bc7_encode_kernel<<<(unsigned)grid, NT, sizeof(Shared), s>>>(P, nullptr, nullptr, 1);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -925,13 +925,14 @@ bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba
 template <bool NORMAL>
 cudaError_t launch_fused(const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
                          int total_tiles, cudaStream_t s) {
-    static std::once_flag once;
-    std::call_once(once, [] {
+    // function attributes are per device: set once on each device that launches
+    static std::once_flag once[64];
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    std::call_once(once[dev & 63], [] {
         cudaFuncSetAttribute(mip_fused_kernel<NORMAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)FUSED_SMEM_BYTES);
     });
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int want = (total_tiles + GROUPS - 1) / GROUPS;  // every group of every CTA gets a tile
     const int grid = want < sms ? want : sms;

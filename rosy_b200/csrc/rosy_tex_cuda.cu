@@ -712,7 +712,7 @@ int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* 
                             d_scratch, static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), true, true);
 }
 
-size_t rosy_tex_batch_scratch_size(int count) { return count > 0 ? mips_batch_desc_bytes(count) : 0; }
+size_t rosy_tex_batch_scratch_size(int count) { return count > 0 ? mips_batch_desc_bytes(count) + bc7_batch_desc_bytes(count) : 0; }
 
 int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
                                  int do_mips, int do_blocks) {
@@ -742,10 +742,29 @@ int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, vo
         g_launches += (uint64_t)n;
     }
     if (do_blocks) {
+        // BC7 textures: one launch for all of them (per quality tier); BC4 / BC5: one launch each
+        std::vector<Bc7BatchItem> bi;
         for (int i = 0; i < count; i++) {
-            int rc = encode_on_stream(mi[i].chain, rs[i], mi[i].d_rgba, mi[i].d_chain, nullptr,
-                                      static_cast<uint8_t*>(items[i].d_blocks), s, false, true);
-            if (rc) return rc;
+            if (rs[i].format == ROSY_TEX_FORMAT_BC7) {
+                Bc7BatchItem b;
+                b.chain = mi[i].chain;
+                b.quality = rs[i].quality;
+                b.d_level0 = rs[i].normal_map ? nullptr : mi[i].d_rgba;
+                b.d_chain = mi[i].d_chain;
+                b.d_blocks = static_cast<uint8_t*>(items[i].d_blocks);
+                bi.push_back(b);
+            } else {
+                int rc = encode_on_stream(mi[i].chain, rs[i], mi[i].d_rgba, mi[i].d_chain, nullptr,
+                                          static_cast<uint8_t*>(items[i].d_blocks), s, false, true);
+                if (rc) return rc;
+            }
+        }
+        if (!bi.empty()) {
+            if (!d_batch_scratch) return fail(ROSY_TEX_ERR_ARG, "null batch scratch");
+            const int n = launch_bc7_batch((int)bi.size(), bi.data(),
+                                           static_cast<uint8_t*>(d_batch_scratch) + mips_batch_desc_bytes(count), s);
+            if (n < 0) return cuda_fail(cudaGetLastError(), "batched BC7 kernel");
+            g_launches += (uint64_t)n;
         }
     }
     return ROSY_TEX_OK;

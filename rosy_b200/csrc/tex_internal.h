@@ -59,6 +59,16 @@ int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const
 // bc7_encode.cu
 int launch_bc7(const Chain& c, int first_level, int num_levels, int quality,
                const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
+// several textures, one launch per quality tier present
+struct Bc7BatchItem {
+    Chain chain;
+    int quality;
+    const uint8_t* d_level0;  // level 0 pixels when they are not in the chain buffer (colour maps), else nullptr
+    const uint8_t* d_chain;
+    uint8_t* d_blocks;
+};
+size_t bc7_batch_desc_bytes(int n);
+int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_t s);
 int bc7_upload_tables();   // per device, once
 int mips_upload_tables();  // per device, once
 

@@ -284,3 +284,36 @@ def test_batched_device_entry_matches_per_texture(tex, synth):
         first = 0 if kind == tex.KIND_NORMAL_MAP else img.size  # colour level 0 is read from the input
         assert (chain[first:] == ref[first:]).all()
         assert (t_blk.cpu().numpy() == dds[tex.DDS_HEADER_BYTES:]).all()
+
+
+@pytest.mark.gpu
+def test_batched_blocks_mixed_tiers_and_formats(tex, synth):
+    """the batched BC7 launch groups textures by quality tier (one launch each) and leaves BC5 / BC4
+    textures to their own launches; CTAs that straddle two textures must not mix them up"""
+    import torch
+
+    dev = torch.device("cuda", 0)
+    specs = [("albedo", 0, 64, 64, tex.KIND_COLOR, tex.FORMAT_BC7, tex.QUALITY_NORMAL),
+             ("albedo", 5, 100, 60, tex.KIND_COLOR, tex.FORMAT_BC7, tex.QUALITY_FAST),
+             ("normal", 1, 128, 64, tex.KIND_NORMAL_MAP, tex.FORMAT_BC5, tex.QUALITY_NORMAL),
+             ("albedo", 7, 256, 128, tex.KIND_COLOR, tex.FORMAT_BC7, tex.QUALITY_NORMAL),
+             ("metal_rough", 2, 64, 192, tex.KIND_METALLIC_ROUGHNESS, tex.FORMAT_BC4, tex.QUALITY_NORMAL),
+             ("random", 3, 68, 68, tex.KIND_COLOR, tex.FORMAT_BC7, tex.QUALITY_HIGH),
+             ("normal", 4, 64, 64, tex.KIND_NORMAL_MAP, tex.FORMAT_BC7, tex.QUALITY_FAST)]
+    keep, entries, want = [], [], []
+    for name, index, w, h, kind, fmt, q in specs:
+        img = synth.make(name, w, h, index)
+        d = tex.desc(w, h, kind, fmt, q, -1)
+        t_in = torch.from_numpy(img.reshape(-1).copy()).to(dev)
+        t_chain = torch.zeros(tex.chain_size(w, h), dtype=torch.uint8, device=dev)
+        t_scr = torch.zeros(tex.device_scratch_size(d), dtype=torch.uint8, device=dev)
+        t_blk = torch.zeros(tex.dds_size(d) - tex.DDS_HEADER_BYTES, dtype=torch.uint8, device=dev)
+        keep.append((t_in, t_chain, t_scr, t_blk))
+        entries.append((d, t_in.data_ptr(), t_chain.data_ptr(), t_scr.data_ptr(), t_blk.data_ptr()))
+        want.append(tex.encode_rgba8(img, kind, fmt, q))
+    batch = tex.make_batch(entries)
+    t_batch = torch.zeros(tex.batch_scratch_size(len(entries)), dtype=torch.uint8, device=dev)
+    tex.encode_batch_device(batch, t_batch.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for (t_in, t_chain, t_scr, t_blk), dds in zip(keep, want):
+        assert (t_blk.cpu().numpy() == dds[tex.DDS_HEADER_BYTES:]).all()

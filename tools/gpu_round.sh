@@ -15,7 +15,7 @@ python tools/profile_counts.py $OUT/${TAG}_launches.csv albedo-2048-bc7-normal 8
 cp profiles/bench_counts.json $OUT/${TAG}_bench_counts.json
 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"; tail -c 3000 $OUT/${TAG}_bench.json
 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>> $OUT/${TAG}_bench.err; echo "ref rc=$?"; tail -c 600 $OUT/${TAG}_bench_ref.json
-ncu --set full --clock-control none --import-source on -k regex:bc7_encode -s 24 -c 2 -f -o $OUT/${TAG}_bc7 $SHORT > $OUT/${TAG}_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:bc7_encode -s 3 -c 1 -f -o $OUT/${TAG}_bc7 $SHORT > $OUT/${TAG}_ncu2.log 2>&1
 echo "bc7 full rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:mip_fused -s 3 -c 1 -f -o $OUT/${TAG}_mip $SHORT > $OUT/${TAG}_ncu3.log 2>&1
 echo "mip full rc=$?"

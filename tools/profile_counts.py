@@ -2,7 +2,7 @@
 into profiles/bench_counts.json: per-launch warp-instruction and DRAM-byte counts that bench.py
 combines with its live CUDA-event durations (roofline.achieved for the issue-bound BC7 kernel).
 
-    python tools/profile_counts.py gpurun_out/r1a_launches.csv albedo-2048-bc7-normal [textures per mip launch]
+    python tools/profile_counts.py gpurun_out/r1a_launches.csv albedo-2048-bc7-normal [textures per batched launch]
 """
 import collections
 import csv
@@ -39,8 +39,9 @@ doc[key] = {
     "source": os.path.basename(path),
     "bc7_source_sha": sha,
     "launches_averaged": len(agg.get("bc7", {}).get("gpu__time_duration.sum", [])),
-    "bc7_warp_inst_per_launch": mean("bc7", "smsp__inst_executed.sum"),
-    "bc7_dram_bytes_per_launch": (mean("bc7", "dram__bytes_read.sum") or 0) + (mean("bc7", "dram__bytes_write.sum") or 0),
+    "bc7_textures_per_launch": tex_per_mip_launch,
+    "bc7_warp_inst_per_texture": (mean("bc7", "smsp__inst_executed.sum") or 0) / tex_per_mip_launch or None,
+    "bc7_dram_bytes_per_texture": ((mean("bc7", "dram__bytes_read.sum") or 0) + (mean("bc7", "dram__bytes_write.sum") or 0)) / tex_per_mip_launch,
     "bc7_ns_per_launch_under_ncu": mean("bc7", "gpu__time_duration.sum"),
     "mip_warp_inst_per_launch": mean("mip", "smsp__inst_executed.sum"),
     "mip_dram_bytes_per_launch": (mean("mip", "dram__bytes_read.sum") or 0) + (mean("mip", "dram__bytes_write.sum") or 0),
