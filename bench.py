@@ -259,6 +259,9 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # NCCL is plumbing here (barrier + MAX of the times): keep its banner off stdout, which carries the JSON line
+        if not os.environ.get("ROSY_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     fmt = {"bc7": T.FORMAT_BC7, "bc5": T.FORMAT_BC5, "bc4": T.FORMAT_BC4}[args.format]
