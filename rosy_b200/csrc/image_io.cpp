@@ -3,8 +3,7 @@
 // Stands in for nvtt::Surface::load (/root/reference/src/Packager/Packager.cpp:222, :269; SURVEY
 // row A3): decode a file to 8-bit RGBA, images without alpha get alpha = 255.  glTF image URIs
 // (src/Packager/Gltf.cpp:98-111) are PNG / JPEG; the FBX path feeds TGA (src/Packager/Fbx.cpp:421-438).
-// Written from the PNG / TGA / PNM specifications (zlib does the inflate); JPEG is not decoded yet
-//  and reports ROSY_TEX_ERR_DECODE.  Raw ".rgba8" files (u32 width, u32 height,
+// Written from the PNG / TGA / PNM specifications (zlib does the inflate); JPEG lives in jpeg_decode.cpp.  Raw ".rgba8" files (u32 width, u32 height,
 // pixels) are accepted for benchmarks.
 #include <ctype.h>
 #include <stdint.h>
@@ -19,6 +18,9 @@
 #include "../../include/rosy_tex_cuda.h"
 
 namespace rosy_tex {
+
+// jpeg_decode.cpp
+int decode_jpeg(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H, std::string& err);
 
 static bool read_file(const char* path, std::vector<uint8_t>& out) {
     FILE* f = fopen(path, "rb");
@@ -326,8 +328,8 @@ int decode_image_memory(const uint8_t* data, size_t len, const char* name_hint, 
     } else if (len >= 2 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) {
         rc = decode_pnm(f, rgba, w, h);
     } else if (len >= 3 && f[0] == 0xFF && f[1] == 0xD8) {
-        err = "JPEG decode is not implemented (DESIGN.md row N2)";
-        return ROSY_TEX_ERR_DECODE;
+        rc = decode_jpeg(f, rgba, w, h, err);
+        if (rc != ROSY_TEX_OK) return rc;
     } else if (ends_with(".rgba8")) {
         if (len >= 8) {
             memcpy(&w, &f[0], 4);

@@ -98,4 +98,29 @@ for k, v in pngs.items():
     out["png_" + k] = v
     out["rgba_" + k] = dec
 np.savez_compressed(os.path.join(HERE, "stb_image_png.npz"), **out)
+
+# ---- JPEG: decoded by the reference tree's stb_image.h (pins rosy_b200/csrc/jpeg_decode.cpp) ----
+rng = np.random.RandomState(7)
+jout = {}
+for (w, h) in [(64, 48), (37, 53), (1, 1), (2, 3), (17, 9), (33, 16)]:
+    img = synth.make("albedo", w, h, 3)[..., :3] if w >= 8 and h >= 8 else rng.randint(0, 255, (h, w, 3), dtype=np.uint8)
+    variants = {
+        "444": dict(subsampling=0), "422": dict(subsampling=1), "420": dict(subsampling=2),
+        "420_prog": dict(subsampling=2, progressive=True), "444_prog_q95": dict(subsampling=0, progressive=True, quality=95),
+        "422_prog_q50": dict(subsampling=1, progressive=True, quality=50), "420_rst": dict(subsampling=2, restart_marker_blocks=3),
+        "420_prog_rst": dict(subsampling=2, progressive=True, restart_marker_rows=1), "gray": dict(gray=True),
+        "gray_prog": dict(gray=True, progressive=True), "420_opt_q30": dict(subsampling=2, optimize=True, quality=30),
+    }
+    for name, kw in variants.items():
+        kw = dict(kw)
+        gray = kw.pop("gray", False)
+        im = Image.fromarray(img).convert("L") if gray else Image.fromarray(img)
+        buf = io.BytesIO()
+        im.save(buf, "JPEG", **({"quality": 85} | kw))
+        data = np.frombuffer(buf.getvalue(), dtype=np.uint8)
+        dec = O.ref_image_load(data.tobytes())
+        assert dec is not None, name
+        jout[f"jpg_{w}x{h}_{name}"] = data
+        jout[f"rgba_{w}x{h}_{name}"] = dec
+np.savez_compressed(os.path.join(HERE, "stb_image_jpeg.npz"), **jout)
 print("golden vectors written:", sorted(os.listdir(HERE)))

@@ -82,6 +82,41 @@ def test_image_loader_matches_reference_stb_image_vectors(tex, tmp_path):
         assert (got == g["rgba_" + k]).all(), k
 
 
+def test_jpeg_loader_matches_reference_stb_image_vectors(tex, tmp_path):
+    """baseline / progressive / restart-interval JPEGs at 4:4:4, 4:2:2, 4:2:0 and greyscale decode to the
+    bytes the reference tree's stb_image.h produces (Surface::load stand-in, SURVEY row A3)"""
+    g = np.load(os.path.join(GOLD, "stb_image_jpeg.npz"))
+    keys = [k[4:] for k in g.files if k.startswith("jpg_")]
+    assert len(keys) >= 60
+    for k in keys:
+        p = tmp_path / (k + ".jpg")
+        p.write_bytes(g["jpg_" + k].tobytes())
+        got = tex.load_image(str(p))
+        assert got.shape == g["rgba_" + k].shape, k
+        assert (got == g["rgba_" + k]).all(), k
+
+
+def test_jpeg_loader_rejects_bad_files(tex, tmp_path):
+    from rosy_b200 import RosyTexError
+
+    g = np.load(os.path.join(GOLD, "stb_image_jpeg.npz"))
+    good = g["jpg_64x48_420"].tobytes()
+    cases = {"truncated_header": good[:20], "no_scan": good[: good.index(b"\xff\xda")] + b"\xff\xd9",
+             "arithmetic": good.replace(b"\xff\xc0", b"\xff\xc9", 1), "twelve_bit": None}
+    sof = good.index(b"\xff\xc0")
+    cases["twelve_bit"] = good[: sof + 4] + bytes([12]) + good[sof + 5 :]
+    for name, data in cases.items():
+        p = tmp_path / (name + ".jpg")
+        p.write_bytes(data)
+        with pytest.raises(RosyTexError) as e:
+            tex.load_image(str(p))
+        assert e.value.status == 2, name
+    # a file cut in the middle of the entropy-coded data still decodes (missing bits read as zero), like stb
+    p = tmp_path / "cut.jpg"
+    p.write_bytes(good[: len(good) * 2 // 3])
+    assert tex.load_image(str(p)).shape == (48, 64, 4)
+
+
 def test_image_loader_formats_and_errors(tex, synth, tmp_path):
     from PIL import Image
     from rosy_b200 import RosyTexError

@@ -19,11 +19,12 @@ def _write_gltf(tmp_path, with_images=True, size=64):
 
     from rosy_b200 import synth
 
-    names = ["base color.png", "mr.v2.png", "normal.png", "emissive.png"]
+    names = ["base color.jpg", "mr.v2.png", "normal.png", "emissive.png"]
     kinds = ["albedo", "metal_rough", "normal", "albedo"]
     if with_images:
         for i, (n, k) in enumerate(zip(names, kinds)):
-            Image.fromarray(synth.make(k, size, size, i)).save(tmp_path / n)
+            im = Image.fromarray(synth.make(k, size, size, i))
+            (im.convert("RGB") if n.endswith(".jpg") else im).save(tmp_path / n)
     doc = {
         "asset": {"version": "2.0"},
         "images": [{"uri": n.replace(" ", "%20")} for n in names],
@@ -57,7 +58,7 @@ def test_gltf_plan_routing_and_names(tmp_path):
     assert plan["reference_calls"] == 6
     jobs = plan["jobs"]
     assert [(j["image_index"], j["image_type"]) for j in jobs] == [(0, 0), (1, 2), (2, 1)]
-    assert [os.path.basename(j["source"]) for j in jobs] == ["base color.png", "mr.v2.png", "normal.png"]
+    assert [os.path.basename(j["source"]) for j in jobs] == ["base color.jpg", "mr.v2.png", "normal.png"]
     # generate_* writes image_path.replace_extension(".dds") (Packager.cpp:231)
     assert [os.path.basename(j["dds"]) for j in jobs] == ["base color.dds", "mr.v2.dds", "normal.dds"]
     assert [j["uses"] for j in jobs] == [2, 2, 2]
@@ -98,7 +99,7 @@ def test_gltf_packager_run(tmp_path, serial, tex, oracle):
 
     for j in manifest["jobs"]:
         dds = np.fromfile(j["dds"], dtype=np.uint8)
-        img = np.asarray(Image.open(j["source"]).convert("RGBA"))
+        img = tex.load_image(j["source"])  # PNG and JPEG: the loader is pinned against stb_image separately
         kind = tex.KIND_NORMAL_MAP if j["image_type"] == 1 else (tex.KIND_METALLIC_ROUGHNESS if j["image_type"] == 2 else tex.KIND_COLOR)
         want = tex.encode_rgba8(img, kind, tex.FORMAT_BC7, tex.QUALITY_NORMAL)
         assert dds.size == want.size and (dds == want).all()
