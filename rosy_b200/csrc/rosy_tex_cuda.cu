@@ -51,14 +51,31 @@ struct Slot {
     bool busy = false;
 };
 
+// A texture for the device workers: host pixels in, DDS bytes out.
 struct Job {
-    std::string path;  // non-empty: file job
-    std::string dds_path;
     rosy_tex_desc desc;
     const uint8_t* rgba = nullptr;
     void* out = nullptr;
     size_t cap = 0;
     size_t* len = nullptr;
+    // file jobs (rosy_tex_submit): rgba / out are pinned buffers of the pool, the .dds is written afterwards
+    bool from_file = false;
+    std::string dds_path;
+};
+
+// Host-side stage of a file job, run by the I/O threads: decode before the device, write after it.
+struct IoTask {
+    enum Type { DECODE, WRITE } type = DECODE;
+    std::string path, dds_path;
+    int kind = 0;
+    void *pin_in = nullptr, *pin_out = nullptr;  // WRITE: buffers to give back to the pool
+    size_t len = 0;
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    bool used = false;
 };
 
 struct State {
@@ -73,6 +90,12 @@ struct State {
     std::deque<Job> queue;
     std::vector<std::thread> workers;
     int running = 0;
+    int pending = 0;  // submitted textures that are not completely done (decode, device, write)
+    // file pipeline: decode / write threads, decoded images waiting for a device slot, pinned staging pool
+    std::deque<IoTask> io_queue;
+    std::vector<std::thread> io_workers;
+    int decoded_inflight = 0, decoded_limit = 4;
+    std::vector<PinBuf> pinned;
     int first_error = 0;
     std::string first_error_msg;
     bool stop = false;
@@ -361,6 +384,8 @@ std::string replace_extension(const std::string& path, const char* ext) {
     return path.substr(0, dot) + ext;
 }
 
+int write_dds_file(const std::string& dds_path, const void* data, size_t len);
+
 // the whole of generate_srgb_texture / generate_normal_map_texture for one file, on one slot
 int run_file(Slot* sl, const std::string& path, int kind, const std::string& dds_path_in) {
     std::vector<uint8_t> rgba;
@@ -375,17 +400,47 @@ int run_file(Slot* sl, const std::string& path, int kind, const std::string& dds
     size_t len = 0;
     if ((rc = run_host(sl, r, WHAT_DDS, rgba.data(), dds.data(), dds.size(), &len))) return rc;
     const std::string dds_path = dds_path_in.empty() ? replace_extension(path, ".dds") : dds_path_in;  // :231
-    const std::string tmp = dds_path + ".tmp";
-    FILE* f = fopen(tmp.c_str(), "wb");
-    if (!f) return fail(ROSY_TEX_ERR_IO, "cannot create '" + tmp + "'");
-    const bool ok = fwrite(dds.data(), 1, len, f) == len;
-    if (fclose(f) != 0 || !ok || rename(tmp.c_str(), dds_path.c_str()) != 0) {
-        remove(tmp.c_str());
-        return fail(ROSY_TEX_ERR_IO, "cannot write '" + dds_path + "'");
-    }
-    return ROSY_TEX_OK;
+    return write_dds_file(dds_path, dds.data(), len);
 }
 
+// ---- pinned staging pool (file pipeline) ----
+void* pin_acquire(State& s, size_t bytes) {
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        PinBuf* best = nullptr;
+        for (PinBuf& b : s.pinned)
+            if (!b.used && b.cap >= bytes && (!best || b.cap < best->cap)) best = &b;
+        if (best) {
+            best->used = true;
+            return best->p;
+        }
+    }
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> g(s.mu);
+    PinBuf b;
+    b.p = p;
+    b.cap = bytes;
+    b.used = true;
+    s.pinned.push_back(b);
+    return p;
+}
+void pin_release_locked(State& s, void* p) {
+    for (PinBuf& b : s.pinned)
+        if (b.p == p) b.used = false;
+}
+
+void note_error_locked(State& s, int rc) {
+    if (rc && !s.first_error) {
+        s.first_error = rc;
+        s.first_error_msg = t_error;
+    }
+}
+
+// device worker: one per queue slot
 void worker_main(Slot* sl) {
     State& s = st();
     for (;;) {
@@ -398,24 +453,138 @@ void worker_main(Slot* sl) {
             s.queue.pop_front();
             s.running++;
         }
-        int rc;
-        if (!job.path.empty()) {
-            rc = run_file(sl, job.path, job.desc.kind, job.dds_path);
-        } else {
-            Resolved r;
-            rc = resolve(&job.desc, r);
-            if (!rc) rc = run_host(sl, r, WHAT_DDS, job.rgba, static_cast<uint8_t*>(job.out), job.cap, job.len);
-        }
+        Resolved r;
+        size_t len_local = 0;
+        int rc = resolve(&job.desc, r);
+        if (!rc)
+            rc = run_host(sl, r, WHAT_DDS, job.rgba, static_cast<uint8_t*>(job.out), job.cap, job.len ? job.len : &len_local);
         {
             std::lock_guard<std::mutex> g(s.mu);
-            if (rc && !s.first_error) {
-                s.first_error = rc;
-                s.first_error_msg = t_error;
-            }
+            note_error_locked(s, rc);
             s.running--;
+            if (job.from_file) {
+                s.decoded_inflight--;
+                if (rc) {
+                    pin_release_locked(s, const_cast<uint8_t*>(job.rgba));
+                    pin_release_locked(s, job.out);
+                    s.pending--;
+                } else {  // the .dds is written by an I/O thread; the slot goes on with the next texture
+                    IoTask t;
+                    t.type = IoTask::WRITE;
+                    t.dds_path = job.dds_path;
+                    t.pin_in = const_cast<uint8_t*>(job.rgba);
+                    t.pin_out = job.out;
+                    t.len = len_local;
+                    s.io_queue.push_front(std::move(t));
+                }
+            } else {
+                s.pending--;
+            }
         }
         s.cv.notify_all();
     }
+}
+
+// the device workers exist once the first texture is queued; call with s.mu held
+void start_workers_locked(State& s) {
+    if (!s.workers.empty()) return;
+    // one worker thread per slot; the queue's slots are separate from the synchronous ones
+    const size_t n = s.slots.size();
+    for (size_t i = 0; i < n; i++) {
+        Slot sl;
+        sl.device = s.slots[i].device;
+        sl.busy = true;  // owned by its worker
+        cudaSetDevice(sl.device);
+        cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking);
+        s.slots.push_back(sl);
+    }
+    for (size_t i = 0; i < n; i++) s.workers.emplace_back(worker_main, &s.slots[n + i]);
+}
+
+int write_dds_file(const std::string& dds_path, const void* data, size_t len) {
+    const std::string tmp = dds_path + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return fail(ROSY_TEX_ERR_IO, "cannot create '" + tmp + "'");
+    const bool ok = fwrite(data, 1, len, f) == len;
+    if (fclose(f) != 0 || !ok || rename(tmp.c_str(), dds_path.c_str()) != 0) {
+        remove(tmp.c_str());
+        return fail(ROSY_TEX_ERR_IO, "cannot write '" + dds_path + "'");
+    }
+    return ROSY_TEX_OK;
+}
+
+// I/O worker: decodes image files into pinned buffers ahead of the device (nvtt::Surface::load,
+// Packager.cpp:222 / :269, for many files at once) and writes finished .dds files behind it.
+void io_main() {
+    State& s = st();
+    for (;;) {
+        IoTask t;
+        {
+            std::unique_lock<std::mutex> g(s.mu);
+            auto runnable = [&]() -> int {
+                for (size_t i = 0; i < s.io_queue.size(); i++)
+                    if (s.io_queue[i].type == IoTask::WRITE || s.decoded_inflight < s.decoded_limit) return (int)i;
+                return -1;
+            };
+            s.cv.wait(g, [&] { return s.stop || runnable() >= 0; });
+            const int i = runnable();
+            if (i < 0) return;  // stop
+            t = std::move(s.io_queue[(size_t)i]);
+            s.io_queue.erase(s.io_queue.begin() + i);
+            if (t.type == IoTask::DECODE) s.decoded_inflight++;
+        }
+        if (t.type == IoTask::WRITE) {
+            const int rc = write_dds_file(t.dds_path, t.pin_out, t.len);
+            std::lock_guard<std::mutex> g(s.mu);
+            note_error_locked(s, rc);
+            pin_release_locked(s, t.pin_in);
+            pin_release_locked(s, t.pin_out);
+            s.pending--;
+        } else {
+            std::vector<uint8_t> rgba;
+            uint32_t w = 0, h = 0;
+            std::string err;
+            int rc = load_image(t.path.c_str(), rgba, w, h, err);
+            if (rc) fail(rc, err);
+            Job j;
+            j.desc = {w, h, t.kind, -1, -1, -1};
+            Resolved r;
+            if (!rc) rc = resolve(&j.desc, r);
+            if (!rc) {
+                j.cap = ROSY_TEX_DDS_HEADER_BYTES + (size_t)make_chain(w, h).total_blocks * block_bytes(r.format);
+                void* pin_in = pin_acquire(s, rgba.size());
+                j.out = pin_acquire(s, j.cap);
+                if (!pin_in || !j.out) {
+                    rc = fail(ROSY_TEX_ERR_NOMEM, "pinned host allocation failed");
+                    std::lock_guard<std::mutex> g(s.mu);
+                    if (pin_in) pin_release_locked(s, pin_in);
+                    if (j.out) pin_release_locked(s, j.out);
+                } else {
+                    memcpy(pin_in, rgba.data(), rgba.size());
+                    j.rgba = static_cast<const uint8_t*>(pin_in);
+                }
+            }
+            std::lock_guard<std::mutex> g(s.mu);
+            if (rc) {
+                note_error_locked(s, rc);
+                s.decoded_inflight--;
+                s.pending--;
+            } else {
+                j.from_file = true;
+                j.dds_path = t.dds_path.empty() ? replace_extension(t.path, ".dds") : t.dds_path;  // Packager.cpp:231
+                s.queue.push_back(std::move(j));
+            }
+        }
+        s.cv.notify_all();
+    }
+}
+
+int io_thread_count() {
+    const char* e = getenv("ROSY_TEX_IO_THREADS");
+    int n = e ? atoi(e) : (int)std::thread::hardware_concurrency();
+    if (n < 1) n = 1;
+    if (n > 32) n = 32;
+    return n;
 }
 
 int enqueue(Job&& job) {
@@ -424,20 +593,33 @@ int enqueue(Job&& job) {
     State& s = st();
     {
         std::lock_guard<std::mutex> g(s.mu);
-        if (s.workers.empty()) {
-            // one worker thread per slot; the queue's slots are separate from the synchronous ones
-            const size_t n = s.slots.size();
-            for (size_t i = 0; i < n; i++) {
-                Slot sl;
-                sl.device = s.slots[i].device;
-                sl.busy = true;  // owned by its worker
-                cudaSetDevice(sl.device);
-                cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking);
-                s.slots.push_back(sl);
-            }
-            for (size_t i = 0; i < n; i++) s.workers.emplace_back(worker_main, &s.slots[n + i]);
-        }
+        start_workers_locked(s);
+        s.pending++;
         s.queue.push_back(std::move(job));
+    }
+    s.cv.notify_all();
+    return ROSY_TEX_OK;
+}
+
+int enqueue_file(const char* path, int kind) {
+    int rc = ensure_init();
+    if (rc) return rc;
+    State& s = st();
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        start_workers_locked(s);
+        if (s.io_workers.empty()) {
+            const int n = io_thread_count();
+            for (int i = 0; i < n; i++) s.io_workers.emplace_back(io_main);
+            // images being decoded or waiting for a device slot: every I/O thread busy plus two per slot
+            s.decoded_limit = n + 2 * (int)s.workers.size();
+        }
+        IoTask t;
+        t.type = IoTask::DECODE;
+        t.path = path;
+        t.kind = kind;
+        s.pending++;
+        s.io_queue.push_back(std::move(t));
     }
     s.cv.notify_all();
     return ROSY_TEX_OK;
@@ -490,8 +672,15 @@ void rosy_tex_shutdown(void) {
     }
     s.cv.notify_all();
     for (std::thread& t : s.workers) t.join();
+    for (std::thread& t : s.io_workers) t.join();
     std::lock_guard<std::mutex> g(s.mu);
     s.workers.clear();
+    s.io_workers.clear();
+    s.io_queue.clear();
+    for (PinBuf& b : s.pinned) cudaFreeHost(b.p);
+    s.pinned.clear();
+    s.pending = 0;
+    s.decoded_inflight = 0;
     for (Slot& sl : s.slots) {
         cudaSetDevice(sl.device);
         if (sl.stream) cudaStreamDestroy(sl.stream);
@@ -613,11 +802,7 @@ int rosy_tex_compress_level_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba
 int rosy_tex_submit(const char* image_path, int kind) {
     if (!image_path) return fail(ROSY_TEX_ERR_ARG, "null path");
     if (kind < 0 || kind > 3) return fail(ROSY_TEX_ERR_ARG, "bad kind");
-    Job j;
-    j.path = image_path;
-    memset(&j.desc, 0, sizeof j.desc);
-    j.desc.kind = kind;
-    return enqueue(std::move(j));
+    return enqueue_file(image_path, kind);
 }
 
 int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
@@ -638,7 +823,7 @@ int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* 
 int rosy_tex_wait_all(void) {
     State& s = st();
     std::unique_lock<std::mutex> g(s.mu);
-    s.cv.wait(g, [&] { return s.queue.empty() && s.running == 0; });
+    s.cv.wait(g, [&] { return s.pending == 0; });
     const int rc = s.first_error;
     if (rc) t_error = s.first_error_msg;
     s.first_error = 0;

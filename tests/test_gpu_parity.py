@@ -317,3 +317,34 @@ def test_batched_blocks_mixed_tiers_and_formats(tex, synth):
     torch.cuda.synchronize()
     for (t_in, t_chain, t_scr, t_blk), dds in zip(keep, want):
         assert (t_blk.cpu().numpy() == dds[tex.DDS_HEADER_BYTES:]).all()
+
+
+@pytest.mark.gpu
+def test_file_queue_many_files_and_one_bad(tex, synth, tmp_path):
+    """rosy_tex_submit: decode threads -> pinned staging -> device slots -> writer threads.  Every good file
+    gets the bytes of the synchronous entry point; a corrupt file is reported by wait_all and leaves no .dds"""
+    from PIL import Image
+
+    from rosy_b200 import RosyTexError
+
+    paths = []
+    for i in range(10):
+        img = synth.make(["albedo", "normal", "metal_rough"][i % 3], 64 + 64 * (i % 3), 128, i)
+        p = tmp_path / (f"t{i}.jpg" if i % 4 == 1 else f"t{i}.png")
+        (Image.fromarray(img[..., :3]) if p.suffix == ".jpg" else Image.fromarray(img)).save(p)
+        paths.append((p, tex.KIND_NORMAL_MAP if i % 3 == 1 else tex.KIND_COLOR))
+    bad = tmp_path / "bad.png"
+    bad.write_bytes(b"\x89PNG\r\n\x1a\n" + b"junk" * 8)
+    for k, (p, kind) in enumerate(paths):
+        if k == 5:
+            tex.submit_file(str(bad), tex.KIND_COLOR)
+        tex.submit_file(str(p), kind)
+    with pytest.raises(RosyTexError) as e:
+        tex.wait_all()
+    assert e.value.status == 2
+    assert not (tmp_path / "bad.dds").exists()
+    for p, kind in paths:
+        want = tex.encode_rgba8(tex.load_image(str(p)), kind)
+        got = np.fromfile(p.with_suffix(".dds"), dtype=np.uint8)
+        assert got.size == want.size and (got == want).all(), p.name
+    tex.wait_all()  # the error was consumed
