@@ -80,7 +80,10 @@ typedef enum rosy_tex_normalize {
  * Environment overrides, read by rosy_tex_init (so the Packager CLI stays flag-free):
  *   ROSY_TEX_DEVICES=0,1,..   ROSY_TEX_QUALITY=fast|normal|high
  *   ROSY_TEX_FORMAT_NORMAL=bc7|bc5   ROSY_TEX_FORMAT_COLOR=bc7   ROSY_TEX_FORMAT_MR=bc7|bc5|bc4
- *   ROSY_TEX_NORMALIZE=unpack|off */
+ *   ROSY_TEX_NORMALIZE=unpack|off
+ *   ROSY_TEX_LINEAR_DATA=1   ROSY_TEX_SRGB_FLAG=1   (opt-in corrections; both change
+ *   bytes versus the reference and are therefore off by default)
+ *   ROSY_TEX_IO_THREADS=n     decode / write threads of the file queue (default: host cores, max 32) */
 typedef struct rosy_tex_config {
     uint32_t struct_size;
     int32_t num_devices;                   /* 0: every visible sm_100 device */
@@ -89,6 +92,14 @@ typedef struct rosy_tex_config {
     int32_t format_for_kind[4];            /* rosy_tex_format per rosy_tex_kind, default BC7 */
     int32_t normalize;                     /* rosy_tex_normalize, default UNPACK */
     int32_t streams_per_device;            /* work-queue depth per device, default 2 */
+    /* -- fields below were added later; struct_size tells which ones the caller knows -- */
+    int32_t linear_data_maps;              /* 1: metallic-roughness and mixmap images are data, not colour: plain box
+                                              filter on the stored values, no toLinearFromSrgb / toSrgb round trip
+                                              (the reference sends them through the sRGB function, Gltf.cpp:252,
+                                              Fbx.cpp:453).  Default 0 = like the reference. */
+    int32_t srgb_flag;                     /* 1: OutputOptions::setSrgbFlag(true): colour maps are written as
+                                              DXGI_FORMAT_BC7_UNORM_SRGB (99).  The reference never sets it
+                                              (Packager.cpp:282) and writes 98.  Default 0. */
 } rosy_tex_config;
 
 /* One texture.  format / quality / normalize < 0 mean "use the configured default". */

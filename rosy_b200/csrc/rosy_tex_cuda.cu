@@ -143,7 +143,11 @@ int init_locked(State& s, const rosy_tex_config* user) {
         memcpy(c.format_for_kind, u.format_for_kind, sizeof c.format_for_kind);
         c.normalize = u.normalize;
         if (u.streams_per_device > 0) c.streams_per_device = u.streams_per_device;
+        c.linear_data_maps = u.linear_data_maps != 0;
+        c.srgb_flag = u.srgb_flag != 0;
     }
+    if (const char* e = getenv("ROSY_TEX_LINEAR_DATA")) c.linear_data_maps = atoi(e) != 0;
+    if (const char* e = getenv("ROSY_TEX_SRGB_FLAG")) c.srgb_flag = atoi(e) != 0;
     static const char* const qn[] = {"fast", "normal", "high"};
     static const char* const fn[] = {"bc7", "bc5", "bc4"};
     static const char* const nn[] = {"off", "unpack"};
@@ -207,8 +211,9 @@ int ensure_init() {
 
 struct Resolved {
     uint32_t w, h;
-    bool normal_map;
+    bool normal_map;  // the chain is a plain box filter of the stored values (+ optional re-normalisation)
     int format, quality, normalize;
+    bool srgb_header;  // dxgiFormat 99 instead of 98
 };
 
 int resolve(const rosy_tex_desc* d, Resolved& r) {
@@ -223,6 +228,13 @@ int resolve(const rosy_tex_desc* d, Resolved& r) {
     r.quality = d->quality >= 0 ? d->quality : (s.inited ? s.cfg.quality : ROSY_TEX_QUALITY_NORMAL);
     r.normalize = d->normalize >= 0 ? d->normalize : (s.inited ? s.cfg.normalize : ROSY_TEX_NORMALIZE_UNPACK);
     if (r.format > 2 || r.quality > 2 || r.normalize > 1) return fail(ROSY_TEX_ERR_ARG, "bad format / quality / normalize");
+    const bool data_kind = d->kind == ROSY_TEX_KIND_METALLIC_ROUGHNESS || d->kind == ROSY_TEX_KIND_MIXMAP;
+    if (data_kind && s.inited && s.cfg.linear_data_maps) {
+        // opt-in (N4): data maps skip the sRGB round trip: the normal-map chain without the re-normalisation
+        r.normal_map = true;
+        r.normalize = ROSY_TEX_NORMALIZE_OFF;
+    }
+    r.srgb_header = s.inited && s.cfg.srgb_flag && r.format == ROSY_TEX_FORMAT_BC7 && !r.normal_map;
     return ROSY_TEX_OK;
 }
 
@@ -250,7 +262,7 @@ void write_dds_header(const Resolved& r, int levels, uint8_t* h) {
     put32(h + 80, 0x4);                                               // DDPF_FOURCC
     memcpy(h + 84, "DX10", 4);
     put32(h + 108, 0x1000 | 0x400000 | 0x8);                          // TEXTURE | MIPMAP | COMPLEX
-    put32(h + 128, r.format == ROSY_TEX_FORMAT_BC7 ? 98u : (r.format == ROSY_TEX_FORMAT_BC5 ? 83u : 80u));
+    put32(h + 128, r.format == ROSY_TEX_FORMAT_BC7 ? (r.srgb_header ? 99u : 98u) : (r.format == ROSY_TEX_FORMAT_BC5 ? 83u : 80u));
     put32(h + 132, 3);                                                // D3D10_RESOURCE_DIMENSION_TEXTURE2D
     put32(h + 140, 1);                                                // arraySize
 }

@@ -245,7 +245,7 @@ long long slot_image(const jvalue& textures, const jvalue* slot) {
 }  // namespace
 
 rosy::result plan_gltf_images(const std::shared_ptr<rosy_logger::log>& l, const std::filesystem::path& gltf_path,
-                              gltf_image_plan& plan) {
+                              gltf_image_plan& plan, bool all_textures) {
     plan = gltf_image_plan{};
     std::ifstream f(gltf_path, std::ios::binary);
     if (!f) {
@@ -289,15 +289,18 @@ rosy::result plan_gltf_images(const std::shared_ptr<rosy_logger::log>& l, const 
         const long long c = pbr ? slot_image(*textures, pbr->get("baseColorTexture")) : -1;
         const long long m = pbr ? slot_image(*textures, pbr->get("metallicRoughnessTexture")) : -1;
         const long long n = slot_image(*textures, mat.get("normalTexture"));
-        const long long idx[3] = {c, m, n};
-        for (int k = 0; k < 3; k++) {
+        const long long e = all_textures ? slot_image(*textures, mat.get("emissiveTexture")) : -1;
+        const long long o = all_textures ? slot_image(*textures, mat.get("occlusionTexture")) : -1;
+        const long long idx[5] = {c, m, n, e, o};
+        static const int list_of[5] = {0, 1, 2, 0, 1};  // emissive is colour, occlusion is data
+        for (int k = 0; k < 5; k++) {
             if (idx[k] < 0) continue;
             if ((size_t)idx[k] >= uris.size()) {
                 l->error(std::format("import - image index {} out of range", idx[k]));
                 return rosy::result::error;
             }
-            lists[k].push_back((uint32_t)idx[k]);
-            plan.reference_calls++;
+            lists[list_of[k]].push_back((uint32_t)idx[k]);
+            if (k < 3) plan.reference_calls++;
         }
     }
     // conditioning order (Gltf.cpp:202-286): colour, metallic, normal; each image once per list, and

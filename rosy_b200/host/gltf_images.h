@@ -48,8 +48,11 @@ struct gltf_image_plan {
 
 // Parse `gltf_path` (JSON .gltf) and fill `plan`.  Errors are logged like the importer does and
 // return rosy::result::error.
+// all_textures (opt-in): also route emissiveTexture (as a colour image) and
+// occlusionTexture (as a metallic-roughness / data image), which the reference never reads (F4).
 [[nodiscard]] rosy::result plan_gltf_images(const std::shared_ptr<rosy_logger::log>& l,
-                                            const std::filesystem::path& gltf_path, gltf_image_plan& plan);
+                                            const std::filesystem::path& gltf_path, gltf_image_plan& plan,
+                                            bool all_textures = false);
 
 // The conditioning step (Gltf.cpp:202-286 with cfg.condition_images): every job through the work
 // queue, one wait at the end.  serial = true calls generate_*_texture one after the other instead,

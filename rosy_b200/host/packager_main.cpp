@@ -1,7 +1,7 @@
 // packager_main.cpp - a small CLI over the mirror, for exercising the boundary by hand:
 //   rosy_packager_tex [--normal|--srgb|--mr] <image> [...]      one generate_* call per image, serial
 //   rosy_packager_tex --queue [--normal|--srgb|--mr] <image> ... every image through the work queue
-//   rosy_packager_tex [--serial] [--dry-run] <file.gltf>          the image part of `Packager.exe <file.gltf>`
+//   rosy_packager_tex [--serial] [--dry-run] [--all-textures] <file.gltf>          the image part of `Packager.exe <file.gltf>`
 //       (Main.cpp:126-174 -> Gltf.cpp:97-286): every material image routed to its function, all in
 //       flight through the work queue (--serial: one after the other like the reference), and a
 //       <file>.textures.json manifest of what the .rsy image table holds; --dry-run prints it only.
@@ -25,7 +25,7 @@ int main(int argc, char** argv) {
         l->error("Need to provide an image path");
         return EXIT_FAILURE;
     }
-    bool queue = false, serial = false, dry_run = false;
+    bool queue = false, serial = false, dry_run = false, all_textures = false;
     int image_type = 0;  // Asset.h:109-112: 0 colour, 1 normal map, 2 metallic-roughness, 3 mixmap
     int done = 0;
     const auto start = std::chrono::system_clock::now();
@@ -36,10 +36,11 @@ int main(int argc, char** argv) {
         if (!std::strcmp(argv[i], "--mr")) { image_type = 2; continue; }
         if (!std::strcmp(argv[i], "--serial")) { serial = true; continue; }
         if (!std::strcmp(argv[i], "--dry-run")) { dry_run = true; continue; }
+        if (!std::strcmp(argv[i], "--all-textures")) { all_textures = true; continue; }  // + emissive, occlusion (opt-in)
         if (std::filesystem::path(argv[i]).extension() == ".gltf") {
             // Main.cpp:10-65 load_gltf, image part
             rosy_packager::gltf_image_plan plan;
-            if (rosy_packager::plan_gltf_images(l, argv[i], plan) != rosy::result::ok) return EXIT_FAILURE;
+            if (rosy_packager::plan_gltf_images(l, argv[i], plan, all_textures) != rosy::result::ok) return EXIT_FAILURE;
             const std::string manifest = rosy_packager::plan_to_json(plan);
             if (dry_run) {
                 std::cout << manifest;

@@ -58,6 +58,8 @@ class Config(C.Structure):
         ("format_for_kind", C.c_int32 * 4),
         ("normalize", C.c_int32),
         ("streams_per_device", C.c_int32),
+        ("linear_data_maps", C.c_int32),
+        ("srgb_flag", C.c_int32),
     ]
 
 
@@ -119,7 +121,8 @@ def desc(width, height, kind=KIND_COLOR, format=-1, quality=-1, normalize=-1):
     return Desc(int(width), int(height), int(kind), int(format), int(quality), int(normalize))
 
 
-def init(devices=None, quality=QUALITY_NORMAL, normalize=NORMALIZE_UNPACK, formats=None, streams_per_device=2):
+def init(devices=None, quality=QUALITY_NORMAL, normalize=NORMALIZE_UNPACK, formats=None, streams_per_device=2,
+         linear_data_maps=False, srgb_flag=False):
     cfg = Config()
     cfg.struct_size = C.sizeof(Config)
     if devices:
@@ -129,6 +132,8 @@ def init(devices=None, quality=QUALITY_NORMAL, normalize=NORMALIZE_UNPACK, forma
     cfg.quality = quality
     cfg.normalize = normalize
     cfg.streams_per_device = streams_per_device
+    cfg.linear_data_maps = int(linear_data_maps)
+    cfg.srgb_flag = int(srgb_flag)
     for k, f in (formats or {}).items():
         cfg.format_for_kind[k] = f
     _check(lib().rosy_tex_init(C.byref(cfg)))

@@ -64,6 +64,17 @@ def test_gltf_plan_routing_and_names(tmp_path):
     assert [j["uses"] for j in jobs] == [2, 2, 2]
 
 
+def test_gltf_all_textures_opt_in(tmp_path):
+    """--all-textures (N4) also routes emissive (colour) and occlusion (data) images"""
+    p, names = _write_gltf(tmp_path, with_images=False)
+    out = subprocess.run([CLI, "--dry-run", "--all-textures", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    plan = json.JSONDecoder().raw_decode(out.stdout[out.stdout.index("{"):])[0]
+    # image 3 is emissive (colour list) and occlusion (data list): the later list wins -> image_type 2
+    assert [(j["image_index"], j["image_type"]) for j in plan["jobs"]] == [(0, 0), (1, 2), (3, 2), (2, 1)]
+    assert plan["reference_calls"] == 6
+
+
 def test_gltf_errors(tmp_path):
     bad = tmp_path / "bad.gltf"
     bad.write_text('{"images": [{"bufferView": 0, "mimeType": "image/png"}]}')

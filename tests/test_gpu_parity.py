@@ -348,3 +348,32 @@ def test_file_queue_many_files_and_one_bad(tex, synth, tmp_path):
         got = np.fromfile(p.with_suffix(".dds"), dtype=np.uint8)
         assert got.size == want.size and (got == want).all(), p.name
     tex.wait_all()  # the error was consumed
+
+
+@pytest.mark.gpu
+def test_opt_in_linear_data_maps_and_srgb_flag(tex, oracle, synth):
+    """N4 (off by default): metallic-roughness maps as data = plain box chain, no sRGB round trip; colour maps
+    with setSrgbFlag(true) = dxgiFormat 99.  Defaults are restored afterwards."""
+    img = synth.make("metal_rough", 128, 64, 5)
+    col = synth.make("albedo", 64, 64, 1)
+    base_mr = tex.encode_rgba8(img, tex.KIND_METALLIC_ROUGHNESS)
+    base_col = tex.encode_rgba8(col, tex.KIND_COLOR)
+    tex.shutdown()
+    try:
+        tex.init(linear_data_maps=True, srgb_flag=True)
+        got = tex.encode_rgba8(img, tex.KIND_METALLIC_ROUGHNESS)
+        want = oracle.generate_texture(img, oracle.KIND_NORMAL, oracle.FMT_BC7, oracle.Q_NORMAL, oracle.NORMALIZE_OFF)
+        assert (got[148:] == want[148:]).all()
+        lv = tex.mips_rgba8(img, tex.KIND_METALLIC_ROUGHNESS)
+        ref = oracle.mip_chain(img, oracle.KIND_NORMAL, oracle.NORMALIZE_OFF)
+        assert all((a == b).all() for a, b in zip(lv, ref))  # exact integer box sums
+        assert int.from_bytes(got[128:132].tobytes(), "little") == 98  # data maps stay UNORM
+        c = tex.encode_rgba8(col, tex.KIND_COLOR)
+        assert int.from_bytes(c[128:132].tobytes(), "little") == 99 and (c[148:] == base_col[148:]).all()
+        if oracle.have_ref_dds():
+            assert oracle.ref_dds_read(c.tobytes())["format"] == 99
+    finally:
+        tex.shutdown()
+        tex.init()
+    assert (tex.encode_rgba8(img, tex.KIND_METALLIC_ROUGHNESS) == base_mr).all()
+    assert (tex.encode_rgba8(col, tex.KIND_COLOR) == base_col).all()
