@@ -82,7 +82,7 @@ static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     uint32_t w = 0, h = 0;
     int depth = 0, ctype = 0, interlace = 0;
     std::vector<uint8_t> idat, plte, trns;
-    bool have_ihdr = false, done = false;
+    bool have_ihdr = false, done = false, cgbi = false;
     while (!done && pos + 12 <= f.size()) {
         const uint32_t len = be32(&f[pos]);
         const uint8_t* type = &f[pos + 4];
@@ -97,6 +97,8 @@ static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
             interlace = body[12];
             if (body[10] != 0 || body[11] != 0 || interlace > 1) return ROSY_TEX_ERR_DECODE;
             have_ihdr = true;
+        } else if (!memcmp(type, "CgBI", 4)) {
+            cgbi = true;  // Apple's variant: raw deflate stream; channels stay as stored, like stb_image's default
         } else if (!memcmp(type, "PLTE", 4)) {
             plte.assign(body, body + len);
         } else if (!memcmp(type, "tRNS", 4)) {
@@ -135,8 +137,22 @@ static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     }
     std::vector<uint8_t> raw(raw_size);
     uLongf got = (uLongf)raw_size;
-    const int zr = uncompress(raw.data(), &got, idat.data(), (uLong)idat.size());
-    if ((zr != Z_OK && zr != Z_BUF_ERROR) || got != raw_size) return ROSY_TEX_ERR_DECODE;
+    if (cgbi) {
+        z_stream zs;
+        memset(&zs, 0, sizeof zs);
+        if (inflateInit2(&zs, -15) != Z_OK) return ROSY_TEX_ERR_DECODE;
+        zs.next_in = idat.data();
+        zs.avail_in = (uInt)idat.size();
+        zs.next_out = raw.data();
+        zs.avail_out = (uInt)raw_size;
+        const int zr = inflate(&zs, Z_FINISH);
+        got = (uLongf)zs.total_out;
+        inflateEnd(&zs);
+        if ((zr != Z_STREAM_END && zr != Z_BUF_ERROR && zr != Z_OK) || got != raw_size) return ROSY_TEX_ERR_DECODE;
+    } else {
+        const int zr = uncompress(raw.data(), &got, idat.data(), (uLong)idat.size());
+        if ((zr != Z_OK && zr != Z_BUF_ERROR) || got != raw_size) return ROSY_TEX_ERR_DECODE;
+    }
     W = w;
     H = h;
     rgba.assign((size_t)w * h * 4, 255);

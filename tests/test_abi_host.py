@@ -174,3 +174,32 @@ def test_compute_entry_points_fail_loudly_without_a_device(tex, synth, tmp_path)
     assert e.value.status == 5
     assert not (tmp_path / "a.dds").exists(), "a failed call must leave no .dds behind"
     assert tex.device_count() == 0
+
+
+def test_png_suite_of_the_reference_tree(tex, oracle):
+    """every PNG of src/libs/stb/tests/pngsuite that the reference's stb_image.h decodes gives the same
+    bytes here (only where the reference tree is present: never on the GPU box)"""
+    import glob
+
+    root = "/root/reference/src/libs/stb/tests/pngsuite"
+    files = sorted(glob.glob(root + "/**/*.png", recursive=True))
+    if not files or not oracle.have_ref_stb():
+        pytest.skip("reference tree not present")
+    from rosy_b200 import RosyTexError
+
+    checked = 0
+    for f in files:
+        with open(f, "rb") as fh:
+            data = fh.read()
+        try:
+            ref = oracle.ref_image_load(data)
+        except Exception:
+            ref = None
+        if ref is None:  # corrupt on purpose (x*.png): must be rejected here too
+            with pytest.raises(RosyTexError):
+                tex.load_image(f)
+            continue
+        got = tex.load_image(f)
+        assert got.shape == ref.shape and (got == ref).all(), f
+        checked += 1
+    assert checked >= 240
