@@ -568,34 +568,51 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     if (warp == 9) {
         // ================================ producer ================================
         if (lane != 0) return;
-        int cur = 0;  // texture cursor: tiles are visited in increasing order
+        int cur = -1;  // texture cursor: tiles are visited in increasing order
+        // the current texture's fields stay in registers; they are re-read only when the run of tiles
+        // crosses into the next texture
+        const MipTex* T = &single;
+        int t_base = 0, t_tiles_x = 1, t_normalize = 0;
+        uint32_t t_w = 0, t_off[7] = {0, 0, 0, 0, 0, 0, 0};
+        uint8_t* t_chain = nullptr;
+        float4* t_top = nullptr;
         for (int it = 0; it < my_tiles; it++) {
             const int t = first_tile + it;
             const int s = it % STAGES;
-            if (it >= STAGES) mbar_wait_relaxed(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
-            const MipTex* T = &single;
-            if (texs) {
-                while (cur + 1 < ntex && t >= tile_base[cur + 1]) cur++;
-                T = texs + cur;
+            int want = texs ? (cur < 0 ? 0 : cur) : 0;
+            if (texs)
+                while (want + 1 < ntex && t >= tile_base[want + 1]) want++;
+            if (want != cur) {
+                cur = want;
+                T = texs ? texs + cur : &single;
+                t_base = T->tile_base;
+                t_tiles_x = T->tiles_x;
+                t_normalize = T->normalize;
+                t_w = T->w;
+                t_chain = T->chainbuf;
+                t_top = T->levels > 7 ? T->tile_top : nullptr;
+#pragma unroll
+                for (int l = 0; l < 7; l++) t_off[l] = (uint32_t)T->lpx[l];
             }
-            const int lt = t - T->tile_base;
-            const int tiles_x = T->tiles_x;
-            const int tile_x = lt % tiles_x, tile_y = lt / tiles_x;
+            const int lt = t - t_base;
+            const int tile_x = lt % t_tiles_x, tile_y = lt / t_tiles_x;
+            if (it >= STAGES) mbar_wait_relaxed(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
+            // the copy first: the barrier's phase cannot complete before the arrive below
+            tma_load_tile(S.tiles[s], &T->tmap, tile_x * TILE, tile_y * TILE, &S.full[s]);
             TileInfo& I = S.info[it % INFO_RING];
-            I.chainbuf = T->chainbuf;
-            I.tile_top = T->levels > 7 ? T->tile_top + (size_t)tile_y * tiles_x + tile_x : nullptr;
-            I.w = T->w;
+            I.chainbuf = t_chain;
+            I.tile_top = t_top ? t_top + (size_t)tile_y * t_tiles_x + tile_x : nullptr;
+            I.w = t_w;
             I.tile_x = tile_x;
             I.tile_y = tile_y;
             I.tex = cur;
-            I.normalize = T->normalize;
+            I.normalize = t_normalize;
 #pragma unroll
-            for (int l = 0; l < 7; l++) I.off[l] = (uint32_t)T->lpx[l];
+            for (int l = 0; l < 7; l++) I.off[l] = t_off[l];
 #pragma unroll
             for (int l = 0; l < 4; l++)
-                I.org[l] = (uint32_t)T->lpx[l] + (uint32_t)(tile_y * (TILE >> l)) * (T->w >> l) + (uint32_t)(tile_x * (TILE >> l));
-            mbar_expect_tx(&S.full[s], TILE_BYTES);
-            tma_load_tile(S.tiles[s], &T->tmap, tile_x * TILE, tile_y * TILE, &S.full[s]);
+                I.org[l] = t_off[l] + (uint32_t)(tile_y * (TILE >> l)) * (t_w >> l) + (uint32_t)(tile_x * (TILE >> l));
+            mbar_expect_tx(&S.full[s], TILE_BYTES);  // release: the descriptor above is visible to the waiters
         }
         return;
     }
