@@ -824,8 +824,10 @@ bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ 
         S.best[11][tid] = 5u;
     }
     const bool search = live && !solid;
-    const int tier = P.tier;
-    const int ls = P.ls_rounds, pbs = P.pb_search;
+    // the job list is the same for every thread of the launch: tier / ls / pbs come from the kernel's
+    // own parameter (uniform), never from a per-texture descriptor, so the job decode stays uniform
+    const int tier = P1.tier;
+    const int ls = P1.ls_rounds, pbs = P1.pb_search;
     // candidate under construction
     uint32_t cq[3][2] = {{0, 0}, {0, 0}, {0, 0}}, cpb = 0, cerr = 0;
     uint64_t cidx = 0, cidx2 = 0;
