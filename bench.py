@@ -356,15 +356,13 @@ def main():
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
     value = world * mpix_step / (ms_step * 1e-3)
-    # per-launch durations: the batched step has ONE mip launch (all n textures) and ONE BC7 launch (BC4/BC5: n launches)
+    # per-launch durations: the batched step has ONE mip launch (all n textures) and ONE encoder launch
     used = [evs if args.per_texture else evs[:1] for evs in kernel_events]
     mip_ms = float(np.mean([ea.elapsed_time(eb) for evs in used for (ea, eb, ec) in evs]))
     enc_ms = float(np.mean([eb.elapsed_time(ec) for evs in used for (ea, eb, ec) in evs]))
     mip_tex_per_launch = 1 if args.per_texture else n
-    # the batched call encodes every BC7 texture of the step in ONE launch (BC4/BC5: one launch per texture)
-    enc_tex_per_launch = n if (not args.per_texture and fmt == T.FORMAT_BC7) else 1
-    if not args.per_texture and fmt != T.FORMAT_BC7:
-        enc_ms /= n
+    # the batched call encodes every texture of the step in ONE launch (per format / BC7 quality tier)
+    enc_tex_per_launch = 1 if args.per_texture else n
     clk = clocks.summary()
 
     # ---------------- e2e leg: host buffers through the C ABI work queue --------------------

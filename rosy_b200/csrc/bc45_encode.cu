@@ -12,12 +12,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "tex_internal.h"
 
 namespace rosy_tex {
 namespace {
 
-constexpr int NT = 256;
+constexpr int NT = 256;  // also the size of the reciprocal table
 
 struct Params {
     Chain chain;
@@ -28,8 +30,26 @@ struct Params {
     uint64_t first_block, num_blocks;
 };
 
-// 16 samples packed 4 per word (texel 4k+j in byte j of v[k]) -> 8-byte alpha-style block
-__device__ __forceinline__ uint2 alpha_block(const uint32_t v[4]) {
+// 16 samples packed 4 per word (texel 4k+j in byte j of v[k]) -> 8-byte alpha-style block.
+//
+// stb__CompressAlphaBlock picks, per sample, ind = floor(a / dist) by three compare-and-subtract
+// steps (a = 7 v + bias, 0 <= a < 8 dist) and maps it to the block's index order
+// {1,7,6,5,4,3,2,0}[ind].  The same integers are produced here with far fewer instructions (the
+// kernel has to encode at HBM speed): the quotient is one multiply by the exact 20-bit reciprocal
+// recip[dist] = floor(2^20 / dist) + 1 (exact because a * dist < 2^20), the sixteen 3-bit quotients
+// are gathered as nibbles of two words, and the index map and the 4-bit -> 3-bit packing are done on
+// eight samples at a time with word-wide logic.
+__device__ __forceinline__ uint32_t map_and_pack8(uint32_t x /* eight quotients, one per nibble */) {
+    // {1,7,6,5,4,3,2,0}[q] = ((8 - q) & 7) ^ (1 if the result is 0 or 1)
+    uint32_t r = (0x88888888u - x) & 0x77777777u;
+    r ^= ~((r >> 1) | (r >> 2)) & 0x11111111u;
+    // nibbles -> 3-bit fields: pairs, then quads, then all eight (24 bits)
+    uint32_t t = (r & 0x07070707u) | ((r >> 1) & 0x38383838u);
+    t = (t & 0x003F003Fu) | ((t >> 2) & 0x0FC00FC0u);
+    return (t & 0x00000FFFu) | ((t >> 4) & 0x00FFF000u);
+}
+
+__device__ __forceinline__ uint2 alpha_block(const uint32_t v[4], const uint32_t* recip) {
     // min / max with packed byte SIMD (stb's `else if` update gives the same mn/mx: a sample
     // that lowers mn can never also raise mx past the first sample)
     uint32_t mn4 = __vminu4(__vminu4(v[0], v[1]), __vminu4(v[2], v[3]));
@@ -38,34 +58,45 @@ __device__ __forceinline__ uint2 alpha_block(const uint32_t v[4]) {
     mx4 = __vmaxu4(mx4, mx4 >> 16);
     const int mn = (int)(__vminu4(mn4, mn4 >> 8) & 255u);
     const int mx = (int)(__vmaxu4(mx4, mx4 >> 8) & 255u);
-    const int dist = mx - mn, dist4 = dist * 4, dist2 = dist * 2;
+    const int dist = mx - mn;
     int bias = dist < 8 ? dist - 1 : dist / 2 + 2;
     bias -= mn * 7;
-    uint64_t bits = 0;
+    const uint32_t M = recip[dist];  // 0 for dist == 0: every quotient is 0, as in stb (a = -1 fails every compare)
+    const uint32_t M7 = 7u * M, biasM = (uint32_t)(bias * (int)M);
+    uint32_t nib[2] = {0u, 0u};
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        int a = (int)((v[i >> 2] >> (8 * (i & 3))) & 255u) * 7 + bias;
-        int ind = 0;
-        if (a >= dist4) {
-            ind = 4;
-            a -= dist4;
-        }
-        if (a >= dist2) {
-            ind += 2;
-            a -= dist2;
-        }
-        if (a >= dist) ind += 1;
-        ind = (-ind) & 7;
-        ind ^= (2 > ind);
-        bits |= (uint64_t)ind << (3 * i);
+        const uint32_t s = __byte_perm(v[i >> 2], 0u, 0x4440 + (i & 3));
+        const uint32_t t = s * M7 + biasM;  // (7 s + bias) * M, below 2^24
+        const int j = i & 7, sh = 20 - 4 * j;
+        nib[i >> 3] |= (sh >= 0 ? t >> sh : t << -sh) & (7u << (4 * j));
     }
-    bits = (bits << 16) | ((uint64_t)mn << 8) | (uint64_t)mx;
-    return make_uint2((uint32_t)bits, (uint32_t)(bits >> 32));
+    const uint32_t lo = map_and_pack8(nib[0]), hi = map_and_pack8(nib[1]);  // 24 bits each
+    // block = mx, mn, then 48 index bits
+    return make_uint2((uint32_t)mx | ((uint32_t)mn << 8) | (lo << 16), (lo >> 16) | (hi << 8));
 }
 
+// One texture (P1, plist == nullptr) or a batch: plist[t] describes texture t, whose blocks are
+// threads base_of[t] .. base_of[t+1]-1 of the launch.
 template <bool BC5>
-__global__ void __launch_bounds__(NT) bc45_encode_kernel(const __grid_constant__ Params P) {
-    const uint64_t b = (uint64_t)blockIdx.x * NT + threadIdx.x;
+__global__ void __launch_bounds__(NT)
+bc45_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ plist,
+                   const uint64_t* __restrict__ base_of, int ntex) {
+    __shared__ uint32_t recip[256];
+    recip[threadIdx.x] = threadIdx.x ? (1u << 20) / threadIdx.x + 1u : 0u;  // NT == 256
+    __syncthreads();
+    uint64_t b = (uint64_t)blockIdx.x * NT + threadIdx.x;
+    const Params* Pp = &P1;
+    if (plist) {
+        int lo = 0, hi = ntex;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (b >= base_of[mid]) lo = mid; else hi = mid;
+        }
+        Pp = plist + lo;
+        b -= base_of[lo];
+    }
+    const Params& P = *Pp;
     if (b >= P.num_blocks) return;
     const uint64_t gb = P.first_block + b;
     int level = P.first_level;
@@ -105,9 +136,9 @@ __global__ void __launch_bounds__(NT) bc45_encode_kernel(const __grid_constant__
         r4[k] = __byte_perm(t0, t1, 0x5410);
         g4[k] = __byte_perm(t0, t1, 0x7632);
     }
-    const uint2 rb = alpha_block(r4);
+    const uint2 rb = alpha_block(r4, recip);
     if (BC5) {
-        const uint2 gbk = alpha_block(g4);
+        const uint2 gbk = alpha_block(g4, recip);
         reinterpret_cast<uint4*>(P.out)[b] = make_uint4(rb.x, rb.y, gbk.x, gbk.y);
     } else {
         reinterpret_cast<uint2*>(P.out)[b] = rb;
@@ -116,9 +147,8 @@ __global__ void __launch_bounds__(NT) bc45_encode_kernel(const __grid_constant__
 
 }  // namespace
 
-int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
-                const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
-    Params P;
+static void fill_params(Params& P, const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
+                        const uint8_t* d_chain, uint8_t* d_blocks) {
     P.chain = c;
     P.level0 = d_level0;
     P.chainbuf = d_chain;
@@ -128,12 +158,64 @@ int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const
     const int last = first_level + num_levels - 1;
     P.num_blocks = c.lv[last].blk_offset + (uint64_t)c.lv[last].bw * c.lv[last].bh - P.first_block;
     P.out = d_blocks + (bc5 ? 16ull : 8ull) * P.first_block;
+}
+
+int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
+                const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
+    Params P;
+    fill_params(P, c, first_level, num_levels, bc5, d_level0, d_chain, d_blocks);
     const unsigned grid = (unsigned)((P.num_blocks + NT - 1) / NT);
     if (bc5)
-        bc45_encode_kernel<true><<<grid, NT, 0, s>>>(P);
+        bc45_encode_kernel<true><<<grid, NT, 0, s>>>(P, nullptr, nullptr, 1);
     else
-        bc45_encode_kernel<false><<<grid, NT, 0, s>>>(P);
+        bc45_encode_kernel<false><<<grid, NT, 0, s>>>(P, nullptr, nullptr, 1);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+size_t bc45_batch_desc_bytes(int n) {
+    return align256((size_t)n * sizeof(Params)) + align256((size_t)(n + 2) * sizeof(uint64_t));
+}
+
+// BC5 / BC4 blocks of n textures (all levels each): one launch per format present.  d_desc:
+// bc45_batch_desc_bytes(n) bytes of device memory that must stay untouched until the launches ran.
+int launch_bc45_batch(int n, const Bc45BatchItem* items, void* d_desc, cudaStream_t s) {
+    int launches = 0;
+    uint8_t* dd = reinterpret_cast<uint8_t*>(d_desc);
+    Params* d_ps = reinterpret_cast<Params*>(dd);
+    uint64_t* d_base = reinterpret_cast<uint64_t*>(dd + align256((size_t)n * sizeof(Params)));
+    std::vector<Params> ps;
+    std::vector<uint64_t> base;
+    size_t used_p = 0, used_b = 0;
+    for (int fmt = 0; fmt < 2; fmt++) {
+        const bool bc5 = fmt == 0;
+        ps.clear();
+        base.clear();
+        uint64_t total = 0;
+        for (int i = 0; i < n; i++) {
+            if (items[i].bc5 != bc5) continue;
+            Params P;
+            fill_params(P, items[i].chain, 0, items[i].chain.levels, bc5, items[i].d_level0, items[i].d_chain, items[i].d_blocks);
+            base.push_back(total);
+            total += P.num_blocks;
+            ps.push_back(P);
+        }
+        if (ps.empty()) continue;
+        base.push_back(total);
+        if (cudaMemcpyAsync(d_ps + used_p, ps.data(), ps.size() * sizeof(Params), cudaMemcpyHostToDevice, s) != cudaSuccess ||
+            cudaMemcpyAsync(d_base + used_b, base.data(), base.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, s) != cudaSuccess)
+            return -1;
+        const unsigned grid = (unsigned)((total + NT - 1) / NT);
+        if (bc5)
+            bc45_encode_kernel<true><<<grid, NT, 0, s>>>(ps[0], d_ps + used_p, d_base + used_b, (int)ps.size());
+        else
+            bc45_encode_kernel<false><<<grid, NT, 0, s>>>(ps[0], d_ps + used_p, d_base + used_b, (int)ps.size());
+        if (cudaGetLastError() != cudaSuccess) return -1;
+        used_p += ps.size();
+        used_b += base.size();
+        launches++;
+    }
+    return launches;
 }
 
 }  // namespace rosy_tex

@@ -909,7 +909,7 @@ int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* 
                             d_scratch, static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), true, true);
 }
 
-size_t rosy_tex_batch_scratch_size(int count) { return count > 0 ? mips_batch_desc_bytes(count) + bc7_batch_desc_bytes(count) : 0; }
+size_t rosy_tex_batch_scratch_size(int count) { return count > 0 ? mips_batch_desc_bytes(count) + bc7_batch_desc_bytes(count) + bc45_batch_desc_bytes(count) : 0; }
 
 int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
                                  int do_mips, int do_blocks) {
@@ -939,28 +939,39 @@ int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, vo
         g_launches += (uint64_t)n;
     }
     if (do_blocks) {
-        // BC7 textures: one launch for all of them (per quality tier); BC4 / BC5: one launch each
+        // one launch for all BC7 textures of a quality tier, one for all BC5, one for all BC4 textures
         std::vector<Bc7BatchItem> bi;
+        std::vector<Bc45BatchItem> ai;
         for (int i = 0; i < count; i++) {
+            const uint8_t* level0 = rs[i].normal_map ? nullptr : mi[i].d_rgba;
             if (rs[i].format == ROSY_TEX_FORMAT_BC7) {
                 Bc7BatchItem b;
                 b.chain = mi[i].chain;
                 b.quality = rs[i].quality;
-                b.d_level0 = rs[i].normal_map ? nullptr : mi[i].d_rgba;
+                b.d_level0 = level0;
                 b.d_chain = mi[i].d_chain;
                 b.d_blocks = static_cast<uint8_t*>(items[i].d_blocks);
                 bi.push_back(b);
             } else {
-                int rc = encode_on_stream(mi[i].chain, rs[i], mi[i].d_rgba, mi[i].d_chain, nullptr,
-                                          static_cast<uint8_t*>(items[i].d_blocks), s, false, true);
-                if (rc) return rc;
+                Bc45BatchItem a;
+                a.chain = mi[i].chain;
+                a.bc5 = rs[i].format == ROSY_TEX_FORMAT_BC5;
+                a.d_level0 = level0;
+                a.d_chain = mi[i].d_chain;
+                a.d_blocks = static_cast<uint8_t*>(items[i].d_blocks);
+                ai.push_back(a);
             }
         }
+        if (!d_batch_scratch) return fail(ROSY_TEX_ERR_ARG, "null batch scratch");
+        uint8_t* desc = static_cast<uint8_t*>(d_batch_scratch) + mips_batch_desc_bytes(count);
         if (!bi.empty()) {
-            if (!d_batch_scratch) return fail(ROSY_TEX_ERR_ARG, "null batch scratch");
-            const int n = launch_bc7_batch((int)bi.size(), bi.data(),
-                                           static_cast<uint8_t*>(d_batch_scratch) + mips_batch_desc_bytes(count), s);
+            const int n = launch_bc7_batch((int)bi.size(), bi.data(), desc, s);
             if (n < 0) return cuda_fail(cudaGetLastError(), "batched BC7 kernel");
+            g_launches += (uint64_t)n;
+        }
+        if (!ai.empty()) {
+            const int n = launch_bc45_batch((int)ai.size(), ai.data(), desc + bc7_batch_desc_bytes(count), s);
+            if (n < 0) return cuda_fail(cudaGetLastError(), "batched BC5 / BC4 kernel");
             g_launches += (uint64_t)n;
         }
     }

@@ -56,6 +56,15 @@ int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream
 // bc45_encode.cu
 int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,
                 const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
+struct Bc45BatchItem {
+    Chain chain;
+    bool bc5;
+    const uint8_t* d_level0;  // level 0 pixels when they are not in the chain buffer (colour maps), else nullptr
+    const uint8_t* d_chain;
+    uint8_t* d_blocks;
+};
+size_t bc45_batch_desc_bytes(int n);
+int launch_bc45_batch(int n, const Bc45BatchItem* items, void* d_desc, cudaStream_t s);
 // bc7_encode.cu
 int launch_bc7(const Chain& c, int first_level, int num_levels, int quality,
                const uint8_t* d_level0, const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s);
