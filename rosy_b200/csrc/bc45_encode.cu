@@ -21,6 +21,31 @@ namespace {
 
 constexpr int NT = 256;  // also the size of the reciprocal table
 
+// floor(2^20 / d) + 1 for d = 1..255 (0 for d = 0): exact reciprocals for quotients a / d with a * d < 2^20
+__device__ const uint32_t g_RECIP20[256] = {
+    0, 1048577, 524289, 349526, 262145, 209716, 174763, 149797, 131073, 116509, 104858, 95326,
+    87382, 80660, 74899, 69906, 65537, 61681, 58255, 55189, 52429, 49933, 47663, 45591,
+    43691, 41944, 40330, 38837, 37450, 36158, 34953, 33826, 32769, 31776, 30841, 29960,
+    29128, 28340, 27595, 26887, 26215, 25576, 24967, 24386, 23832, 23302, 22796, 22311,
+    21846, 21400, 20972, 20561, 20165, 19785, 19419, 19066, 18725, 18397, 18079, 17773,
+    17477, 17190, 16913, 16645, 16385, 16132, 15888, 15651, 15421, 15197, 14980, 14769,
+    14564, 14365, 14170, 13982, 13798, 13618, 13444, 13274, 13108, 12946, 12788, 12634,
+    12484, 12337, 12193, 12053, 11916, 11782, 11651, 11523, 11398, 11276, 11156, 11038,
+    10923, 10811, 10700, 10592, 10486, 10382, 10281, 10181, 10083, 9987, 9893, 9800,
+    9710, 9620, 9533, 9447, 9363, 9280, 9199, 9119, 9040, 8963, 8887, 8812,
+    8739, 8666, 8595, 8526, 8457, 8389, 8323, 8257, 8193, 8129, 8066, 8005,
+    7944, 7885, 7826, 7768, 7711, 7654, 7599, 7544, 7490, 7437, 7385, 7333,
+    7282, 7232, 7183, 7134, 7085, 7038, 6991, 6945, 6899, 6854, 6809, 6766,
+    6722, 6679, 6637, 6595, 6554, 6513, 6473, 6433, 6394, 6356, 6317, 6279,
+    6242, 6205, 6169, 6133, 6097, 6062, 6027, 5992, 5958, 5925, 5891, 5858,
+    5826, 5794, 5762, 5730, 5699, 5668, 5638, 5608, 5578, 5549, 5519, 5490,
+    5462, 5434, 5406, 5378, 5350, 5323, 5296, 5270, 5243, 5217, 5191, 5166,
+    5141, 5116, 5091, 5066, 5042, 5018, 4994, 4970, 4947, 4923, 4900, 4878,
+    4855, 4833, 4810, 4789, 4767, 4745, 4724, 4703, 4682, 4661, 4640, 4620,
+    4600, 4579, 4560, 4540, 4520, 4501, 4482, 4463, 4444, 4425, 4406, 4388,
+    4370, 4351, 4333, 4316, 4298, 4280, 4263, 4246, 4229, 4212, 4195, 4178,
+    4162, 4145, 4129, 4113};
+
 struct Params {
     Chain chain;
     const uint8_t* level0;
@@ -49,15 +74,27 @@ __device__ __forceinline__ uint32_t map_and_pack8(uint32_t x /* eight quotients,
     return (t & 0x00000FFFu) | ((t >> 4) & 0x00FFF000u);
 }
 
+__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;  // kept opaque so that the compiler does not re-factor the folded constants back into three multiplies
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 __device__ __forceinline__ uint2 alpha_block(const uint32_t v[4], const uint32_t* recip) {
-    // min / max with packed byte SIMD (stb's `else if` update gives the same mn/mx: a sample
-    // that lowers mn can never also raise mx past the first sample)
-    uint32_t mn4 = __vminu4(__vminu4(v[0], v[1]), __vminu4(v[2], v[3]));
-    uint32_t mx4 = __vmaxu4(__vmaxu4(v[0], v[1]), __vmaxu4(v[2], v[3]));
-    mn4 = __vminu4(mn4, mn4 >> 16);
-    mx4 = __vmaxu4(mx4, mx4 >> 16);
-    const int mn = (int)(__vminu4(mn4, mn4 >> 8) & 255u);
-    const int mx = (int)(__vmaxu4(mx4, mx4 >> 8) & 255u);
+    // the sixteen samples as integers (needed for the multiplies anyway), min / max by 3-input min / max
+    // (stb's `else if` update gives the same mn/mx: a sample that lowers mn can never also raise mx past
+    // the first sample)
+    int sv[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) sv[i] = (int)__byte_perm(v[i >> 2], 0u, 0x4440 + (i & 3));
+    int mn = sv[0], mx = sv[0];
+#pragma unroll
+    for (int i = 1; i < 15; i += 2) {
+        mn = __vimin3_s32(mn, sv[i], sv[i + 1]);
+        mx = __vimax3_s32(mx, sv[i], sv[i + 1]);
+    }
+    mn = min(mn, sv[15]);
+    mx = max(mx, sv[15]);
     const int dist = mx - mn;
     int bias = dist < 8 ? dist - 1 : dist / 2 + 2;
     bias -= mn * 7;
@@ -66,8 +103,7 @@ __device__ __forceinline__ uint2 alpha_block(const uint32_t v[4], const uint32_t
     uint32_t nib[2] = {0u, 0u};
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        const uint32_t s = __byte_perm(v[i >> 2], 0u, 0x4440 + (i & 3));
-        const uint32_t t = s * M7 + biasM;  // (7 s + bias) * M, below 2^24
+        const uint32_t t = mad_u32((uint32_t)sv[i], M7, biasM);  // (7 s + bias) * M, below 2^24
         const int j = i & 7, sh = 20 - 4 * j;
         nib[i >> 3] |= (sh >= 0 ? t >> sh : t << -sh) & (7u << (4 * j));
     }
@@ -83,7 +119,7 @@ __global__ void __launch_bounds__(NT)
 bc45_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ plist,
                    const uint64_t* __restrict__ base_of, int ntex) {
     __shared__ uint32_t recip[256];
-    recip[threadIdx.x] = threadIdx.x ? (1u << 20) / threadIdx.x + 1u : 0u;  // NT == 256
+    recip[threadIdx.x] = g_RECIP20[threadIdx.x];  // NT == 256
     __syncthreads();
     uint64_t b = (uint64_t)blockIdx.x * NT + threadIdx.x;
     const Params* Pp = &P1;
@@ -99,9 +135,10 @@ bc45_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__
     const Params& P = *Pp;
     if (b >= P.num_blocks) return;
     const uint64_t gb = P.first_block + b;
+    // three blocks in four belong to the first level: walk up only as far as needed
     int level = P.first_level;
-    for (int l = P.first_level + 1; l < P.first_level + P.num_levels; l++)
-        if (gb >= P.chain.lv[l].blk_offset) level = l;
+    const int end_level = P.first_level + P.num_levels;
+    while (level + 1 < end_level && gb >= P.chain.lv[level + 1].blk_offset) level++;
     const Level lv = P.chain.lv[level];
     const uint32_t lb = (uint32_t)(gb - lv.blk_offset);
     const uint32_t bx = lb % lv.bw, by = lb / lv.bw;
