@@ -83,7 +83,11 @@ typedef enum rosy_tex_normalize {
  *   ROSY_TEX_NORMALIZE=unpack|off
  *   ROSY_TEX_LINEAR_DATA=1   ROSY_TEX_SRGB_FLAG=1   (opt-in corrections; both change
  *   bytes versus the reference and are therefore off by default)
- *   ROSY_TEX_IO_THREADS=n     decode / write threads of the file queue (default: host cores, max 32) */
+ *   ROSY_TEX_IO_THREADS=n     decode / write threads of the file queue (default: host cores, max 32)
+ *   ROSY_TEX_STAGING_MB=n     pinned staging budget of the file queue (default 4096)
+ *   ROSY_TEX_QUEUE_BATCH=0    work queue: one texture per pass whatever its size (default 1: a backlog of
+ *                             textures of at most 512x512 pixels is taken up to 64 at a time / 4 Mpix and goes
+ *                             through one set of kernel launches; the bytes are the same either way) */
 typedef struct rosy_tex_config {
     uint32_t struct_size;
     int32_t num_devices;                   /* 0: every visible sm_100 device */

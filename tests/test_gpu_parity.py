@@ -215,6 +215,56 @@ def test_work_queue_matches_sync_and_is_deterministic(tex, synth):
         assert (out == tex.encode_rgba8(img, kind)).all()
 
 
+def test_work_queue_batches_small_textures_identically(tex, synth):
+    """A backlog of small textures goes through the queue several per launch (worker_main /
+    run_host_batch): mixed extents (ragged, 1x1, non power of two), kinds, formats and quality
+    tiers must come back with exactly the bytes of the synchronous single-texture call, twice."""
+    rng = np.random.RandomState(11)
+    sizes = [(256, 256), (512, 512), (100, 60), (4, 4), (1, 1), (7, 300), (1024, 1024), (64, 192), (333, 129), (16, 16)]
+    cases = []
+    for i in range(90):
+        w, h = sizes[rng.randint(len(sizes))]
+        k = rng.randint(3)
+        if k == 1:
+            img, kind = synth.normal(w, h, i), tex.KIND_NORMAL_MAP
+            fmt = [tex.FORMAT_BC7, tex.FORMAT_BC5][rng.randint(2)]
+        elif k == 2:
+            img, kind = synth.make("metal_rough", w, h, i), tex.KIND_METALLIC_ROUGHNESS
+            fmt = [tex.FORMAT_BC7, tex.FORMAT_BC4][rng.randint(2)]
+        else:
+            img, kind, fmt = synth.albedo(w, h, i), tex.KIND_COLOR, tex.FORMAT_BC7
+        cases.append((img, kind, fmt, int(rng.randint(3))))
+    cases.insert(40, (synth.albedo(2048, 1024, 5), tex.KIND_COLOR, tex.FORMAT_BC7, 1))  # too large for a batch: alone
+    want = [tex.encode_rgba8(img, kind, fmt, q) for img, kind, fmt, q in cases]
+    for _ in range(2):
+        q = tex.Pending()
+        for img, kind, fmt, qu in cases:
+            q.submit(img, kind, fmt, qu)
+        outs = q.wait_all()
+        assert len(outs) == len(want)
+        for i, (o, w_) in enumerate(zip(outs, want)):
+            assert o.size == w_.size and (o == w_).all(), f"texture {i} {cases[i][0].shape} differs from the synchronous call"
+
+
+def test_work_queue_batch_member_error_is_isolated(tex, synth):
+    """one member of a batch with an output buffer that is too small: wait_all reports it, the others are complete"""
+    import ctypes as C
+
+    L = tex.lib()
+    imgs = [synth.albedo(128, 128, i) for i in range(12)]
+    descs = [tex.desc(128, 128, tex.KIND_COLOR, tex.FORMAT_BC7, 1, -1) for _ in imgs]
+    outs = [np.zeros(tex.dds_size(d), np.uint8) for d in descs]
+    lens = [C.c_size_t() for _ in imgs]
+    for i, (img, d, o, n) in enumerate(zip(imgs, descs, outs, lens)):
+        cap = 200 if i == 5 else o.size
+        assert L.rosy_tex_submit_rgba8(C.byref(d), img.ctypes.data, o.ctypes.data, cap, C.byref(n)) == 0
+    assert L.rosy_tex_wait_all() != 0
+    assert L.rosy_tex_wait_all() == 0
+    for i, (img, o) in enumerate(zip(imgs, outs)):
+        if i != 5:
+            assert (o == tex.encode_rgba8(img, tex.KIND_COLOR, tex.FORMAT_BC7, 1)).all(), i
+
+
 def test_size_independent_properties_at_full_size(tex, oracle, synth):
     """config sizes the oracle is too slow for: structure + decodability + PSNR floor + idempotent"""
     img = synth.normal(2048, 2048, 1)
