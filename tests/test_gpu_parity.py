@@ -279,6 +279,49 @@ def test_size_independent_properties_at_full_size(tex, oracle, synth):
     assert oracle.psnr(want0, dec) > 38.0
 
 
+def _level_blocks(dds, w, h, bs, levels):
+    """-> per level (blocks_y, blocks_x, bs) views of the payload of a .dds"""
+    out, off = [], 148
+    for k in range(levels):
+        lw, lh = max(1, w >> k), max(1, h >> k)
+        bx, by = (lw + 3) // 4, (lh + 3) // 4
+        out.append(dds[off : off + bx * by * bs].reshape(by, bx, bs))
+        off += bx * by * bs
+    return out
+
+
+@pytest.mark.parametrize("size", [(8192, 8192), (16384, 4096), (4096, 16384)])
+@pytest.mark.parametrize("case", ["bc7_colour", "bc5_normal", "bc4_data"])
+def test_maximum_sizes_by_periodicity(tex, synth, size, case):
+    """Sizes the oracle cannot reach in seconds (config 4's 8192^2 and beyond): a texture made of
+    512x512 repeats of a base image has mips and blocks that are the same repeats of the base
+    image's (box filter and block search are local, 512 is a multiple of every footprint), for
+    levels 0..7 (base extent >= 4).  The base image's output is checked against the oracle by the
+    tests above; this one checks addressing and tiling over > 2^26 pixels."""
+    w, h = size
+    if case == "bc7_colour":
+        base, kind, fmt, bs, q = synth.albedo(512, 512, 7), tex.KIND_COLOR, tex.FORMAT_BC7, 16, 0
+    elif case == "bc5_normal":
+        base, kind, fmt, bs, q = synth.normal(512, 512, 1), tex.KIND_NORMAL_MAP, tex.FORMAT_BC5, 16, 1
+    else:
+        base, kind, fmt, bs, q = synth.make("metal_rough", 512, 512, 2), tex.KIND_METALLIC_ROUGHNESS, tex.FORMAT_BC4, 8, 1
+    big = np.ascontiguousarray(np.tile(base, (h // 512, w // 512, 1)))
+    small = _level_blocks(tex.encode_rgba8(base, kind, fmt, q), 512, 512, bs, 8)
+    got = tex.encode_rgba8(big, kind, fmt, q)
+    levels = tex.count_mipmaps(w, h)
+    assert got.size == tex.dds_size(tex.desc(w, h, kind, fmt, q, -1))
+    large = _level_blocks(got, w, h, bs, levels)
+    for k in range(8):
+        want = np.tile(small[k], (h // 512, w // 512, 1))
+        assert large[k].shape == want.shape
+        assert (large[k] == want).all(), f"level {k} is not the periodic repeat of the base image's level"
+    # below the period: every level of a periodic image stays periodic down to 1 texel per period
+    chain = tex.mips_rgba8(big, kind)
+    base_chain = tex.mips_rgba8(base, kind)
+    for k in range(10):
+        assert (chain[k] == np.tile(base_chain[k], (h // 512, w // 512, 1))).all(), f"mip level {k}"
+
+
 @pytest.mark.parametrize("size", [(2048, 2048), (4096, 64), (64, 4096), (192, 320), (4096, 4096), (2048, 1024)])
 def test_fused_mip_kernel_shapes(tex, oracle, synth, size):
     """TMA-fused kernel: tails that go through global scratch (4096^2), 1-tile-wide chains, odd tile
