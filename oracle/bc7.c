@@ -418,29 +418,20 @@ static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, 
         tr = tr + C[a][a];
         if (C[a][a] > C[best][best]) best = a;
     }
-    float fn = (float)n;
-    *tr_n = tr / fn;
+    /* 1/n is rounded once and multiplied in (n is a property of the partition, not of the block) */
+    const float rn = 1.0f / (float)n;
+    *tr_n = tr * rn;
     *lam_n = 0.0f;
     if (tr == 0.0f) return;
-    float v[4], w[4], m = 0.0f;
-    for (int a = 0; a < nc; a++) {
-        v[a] = C[a][best];
-        float f = fabsf(v[a]);
-        if (f > m) m = f;
-    }
-    float r = 1.0f / m;
-    for (int a = 0; a < nc; a++) v[a] = v[a] * r;
-    m = 0.0f;
+    /* one power iteration from the covariance column with the largest diagonal, no rescaling:
+     * |C| <= n^2 * 255^2 / 4 < 2^22, so |w| < 2^46, |C w| < 2^70 and the sums below stay < 2^118 */
+    float v[4], w[4];
+    for (int a = 0; a < nc; a++) v[a] = C[a][best];
     for (int a = 0; a < nc; a++) {
         float s = 0.0f;
         for (int b = 0; b < nc; b++) s = s + C[a][b] * v[b];
         w[a] = s;
-        float f = fabsf(s);
-        if (f > m) m = f;
     }
-    if (m == 0.0f) return;
-    r = 1.0f / m;
-    for (int a = 0; a < nc; a++) w[a] = w[a] * r;
     float wu = 0.0f, ww = 0.0f;
     for (int a = 0; a < nc; a++) {
         float s = 0.0f;
@@ -448,10 +439,11 @@ static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, 
         wu = wu + w[a] * s;
         ww = ww + w[a] * w[a];
     }
+    if (ww == 0.0f) return;
     float lam = wu / ww;
     if (lam > tr) lam = tr;
     if (lam < 0.0f) lam = 0.0f;
-    *lam_n = lam / fn;
+    *lam_n = lam * rn;
 }
 
 /* Best-first list of partitions.  Entries are ordered by the key

@@ -53,6 +53,10 @@ __constant__ uint16_t c_P3M1[64], c_P3M2[64];  // 3-subset partitions as 16-bit 
 __constant__ uint8_t c_ANCHOR2[64], c_ANCHOR3A[64], c_ANCHOR3B[64];
 __constant__ uint2 c_JOBS[3][MAXJOBS];       // per quality tier
 __constant__ int c_NJOBS[3];
+// 1/n rounded to fp32 (the oracle's 1.0f / (float)n), n = texels of a subset
+__constant__ float c_RCPN[17] = {0.0f, 1.0f / 1.0f, 1.0f / 2.0f, 1.0f / 3.0f, 1.0f / 4.0f, 1.0f / 5.0f, 1.0f / 6.0f,
+                                 1.0f / 7.0f, 1.0f / 8.0f, 1.0f / 9.0f, 1.0f / 10.0f, 1.0f / 11.0f, 1.0f / 12.0f,
+                                 1.0f / 13.0f, 1.0f / 14.0f, 1.0f / 15.0f, 1.0f / 16.0f};
 
 // ---- job encoding (built on the host, bc7_upload_tables) ---------------------------------------
 enum { JOB_PREP_P3 = 0, JOB_FIT = 1, JOB_EST = 2 };
@@ -450,29 +454,20 @@ __device__ __forceinline__ void subset_line_stats(int n, const int S1[4], const 
             for (int b = 0; b < NC; b++) v[b] = C[b][a];
         }
     }
-    const float fn = (float)n;
-    tr_n = tr / fn;
+    // 1/n comes rounded once from a table (n is a property of the partition: uniform over the warp)
+    const float rn = c_RCPN[n];
+    tr_n = tr * rn;
     lam_n = 0.0f;
     if (tr == 0.0f) return;
-    float w[4], m = 0.0f;
-#pragma unroll
-    for (int a = 0; a < NC; a++) m = fmaxf(m, fabsf(v[a]));
-    float r = 1.0f / m;
-#pragma unroll
-    for (int a = 0; a < NC; a++) v[a] = v[a] * r;
-    m = 0.0f;
+    // one power iteration, no rescaling: |C| < 2^22, |w| < 2^46, |C w| < 2^70, sums < 2^118
+    float w[4];
 #pragma unroll
     for (int a = 0; a < NC; a++) {
         float s = 0.0f;
 #pragma unroll
         for (int b = 0; b < NC; b++) s = s + C[a][b] * v[b];
         w[a] = s;
-        m = fmaxf(m, fabsf(s));
     }
-    if (m == 0.0f) return;
-    r = 1.0f / m;
-#pragma unroll
-    for (int a = 0; a < NC; a++) w[a] = w[a] * r;
     float wu = 0.0f, ww = 0.0f;
 #pragma unroll
     for (int a = 0; a < NC; a++) {
@@ -482,10 +477,11 @@ __device__ __forceinline__ void subset_line_stats(int n, const int S1[4], const 
         wu = wu + w[a] * s;
         ww = ww + w[a] * w[a];
     }
+    if (ww == 0.0f) return;
     float lam = wu / ww;
     lam = lam > tr ? tr : lam;
     lam = lam < 0.0f ? 0.0f : lam;
-    lam_n = lam / fn;
+    lam_n = lam * rn;
 }
 
 struct TopList {
