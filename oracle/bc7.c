@@ -340,34 +340,40 @@ static void fit_subset(const uint8_t px[16][4], int mask, const fit_cfg* cfg, co
         float t[4], m = 0.0f;
         for (int a = 0; a < nc; a++) {
             float s = 0.0f;
-            for (int b = 0; b < nc; b++) s = s + C[a][b] * v[b];
+            for (int b = 0; b < nc; b++) s = fmaf(C[a][b], v[b], s);
             t[a] = s;
             float f = fabsf(s);
             if (f > m) m = f;
         }
         if (m == 0.0f) break;
-        float r = 1.0f / m;
+        /* rescale by the power of two that brings the largest component into [1, 2): exact */
+        uint32_t mb, rb;
+        memcpy(&mb, &m, 4);
+        rb = 0x7F000000u - (mb & 0x7F800000u);
+        float r;
+        memcpy(&r, &rb, 4);
         for (int a = 0; a < nc; a++) v[a] = t[a] * r;
     }
     float len2 = 0.0f;
-    for (int c = 0; c < nc; c++) len2 = len2 + v[c] * v[c];
+    for (int c = 0; c < nc; c++) len2 = fmaf(v[c], v[c], len2);
     float rl = 1.0f / sqrtf(len2);
     for (int c = 0; c < nc; c++) v[c] = v[c] * rl;
     /* 3. project, extremes along the axis */
-    float mean[4], fn = (float)n;
-    for (int c = 0; c < nc; c++) mean[c] = (float)S1[c] / fn;
+    float mean[4];
+    const float rn = 1.0f / (float)n;
+    for (int c = 0; c < nc; c++) mean[c] = (float)S1[c] * rn;
     float tmin = 3.0e38f, tmax = -3.0e38f;
     for (int i = 0; i < 16; i++) {
         if (!((mask >> i) & 1)) continue;
         float t = 0.0f;
-        for (int c = 0; c < nc; c++) t = t + ((float)px[i][c] - mean[c]) * v[c];
+        for (int c = 0; c < nc; c++) t = fmaf((float)px[i][c] - mean[c], v[c], t);
         if (t < tmin) tmin = t;
         if (t > tmax) tmax = t;
     }
     float lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
     for (int c = 0; c < nc; c++) {
-        lo[c] = clampf(mean[c] + tmin * v[c], 0.0f, 255.0f);
-        hi[c] = clampf(mean[c] + tmax * v[c], 0.0f, 255.0f);
+        lo[c] = clampf(fmaf(tmin, v[c], mean[c]), 0.0f, 255.0f);
+        hi[c] = clampf(fmaf(tmax, v[c], mean[c]), 0.0f, 255.0f);
     }
     /* 4/5. quantise + evaluate */
     memset(out, 0, sizeof *out);
@@ -429,15 +435,15 @@ static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, 
     for (int a = 0; a < nc; a++) v[a] = C[a][best];
     for (int a = 0; a < nc; a++) {
         float s = 0.0f;
-        for (int b = 0; b < nc; b++) s = s + C[a][b] * v[b];
+        for (int b = 0; b < nc; b++) s = fmaf(C[a][b], v[b], s);
         w[a] = s;
     }
     float wu = 0.0f, ww = 0.0f;
     for (int a = 0; a < nc; a++) {
         float s = 0.0f;
-        for (int b = 0; b < nc; b++) s = s + C[a][b] * w[b];
-        wu = wu + w[a] * s;
-        ww = ww + w[a] * w[a];
+        for (int b = 0; b < nc; b++) s = fmaf(C[a][b], w[b], s);
+        wu = fmaf(w[a], s, wu);
+        ww = fmaf(w[a], w[a], ww);
     }
     if (ww == 0.0f) return;
     float lam = wu / ww;

@@ -197,32 +197,33 @@ __device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, 
         for (int a = 0; a < NC; a++) {
             float s = 0.0f;
 #pragma unroll
-            for (int b = 0; b < NC; b++) s = s + C[a][b] * v[b];
+            for (int b = 0; b < NC; b++) s = __fmaf_rn(C[a][b], v[b], s);
             t[a] = s;
             m = fmaxf(m, fabsf(s));
         }
         if (m == 0.0f) break;
-        const float r = 1.0f / m;
+        // rescale by the power of two that brings the largest component into [1, 2): exact
+        const float r = __uint_as_float(0x7F000000u - (__float_as_uint(m) & 0x7F800000u));
 #pragma unroll
         for (int a = 0; a < NC; a++) v[a] = t[a] * r;
     }
     float len2 = 0.0f;
 #pragma unroll
-    for (int c = 0; c < NC; c++) len2 = len2 + v[c] * v[c];
+    for (int c = 0; c < NC; c++) len2 = __fmaf_rn(v[c], v[c], len2);
     const float rl = 1.0f / sqrtf(len2);
 #pragma unroll
     for (int c = 0; c < NC; c++) v[c] = v[c] * rl;
     float mean[NC];
-    const float fn = (float)n;
+    const float rn = 1.0f / (float)n;
 #pragma unroll
-    for (int c = 0; c < NC; c++) mean[c] = (float)S1[c] / fn;
+    for (int c = 0; c < NC; c++) mean[c] = (float)S1[c] * rn;
     float tmin = 3.0e38f, tmax = -3.0e38f;
 #pragma unroll 4
     for (int i = 0; i < 16; i++) {
         const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
         float t = 0.0f;
 #pragma unroll
-        for (int c = 0; c < NC; c++) t = t + ((float)((p >> (8 * c)) & 255u) - mean[c]) * v[c];
+        for (int c = 0; c < NC; c++) t = __fmaf_rn((float)((p >> (8 * c)) & 255u) - mean[c], v[c], t);
         if ((mask >> i) & 1u) {
             tmin = t < tmin ? t : tmin;
             tmax = t > tmax ? t : tmax;
@@ -231,8 +232,8 @@ __device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, 
 #pragma unroll
     for (int c = 0; c < 4; c++) {
         if (c < NC) {
-            P.lo[c] = clampf(mean[c] + tmin * v[c], 0.0f, 255.0f);
-            P.hi[c] = clampf(mean[c] + tmax * v[c], 0.0f, 255.0f);
+            P.lo[c] = clampf(__fmaf_rn(tmin, v[c], mean[c]), 0.0f, 255.0f);
+            P.hi[c] = clampf(__fmaf_rn(tmax, v[c], mean[c]), 0.0f, 255.0f);
             P.S1[c] = S1[c];
         } else {
             P.lo[c] = P.hi[c] = 0.0f;
@@ -465,7 +466,7 @@ __device__ __forceinline__ void subset_line_stats(int n, const int S1[4], const 
     for (int a = 0; a < NC; a++) {
         float s = 0.0f;
 #pragma unroll
-        for (int b = 0; b < NC; b++) s = s + C[a][b] * v[b];
+        for (int b = 0; b < NC; b++) s = __fmaf_rn(C[a][b], v[b], s);
         w[a] = s;
     }
     float wu = 0.0f, ww = 0.0f;
@@ -473,9 +474,9 @@ __device__ __forceinline__ void subset_line_stats(int n, const int S1[4], const 
     for (int a = 0; a < NC; a++) {
         float s = 0.0f;
 #pragma unroll
-        for (int b = 0; b < NC; b++) s = s + C[a][b] * w[b];
-        wu = wu + w[a] * s;
-        ww = ww + w[a] * w[a];
+        for (int b = 0; b < NC; b++) s = __fmaf_rn(C[a][b], w[b], s);
+        wu = __fmaf_rn(w[a], s, wu);
+        ww = __fmaf_rn(w[a], w[a], ww);
     }
     if (ww == 0.0f) return;
     float lam = wu / ww;
