@@ -262,20 +262,31 @@ __device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t 
         P[j] = rb | (ga << 8);
         K[j] = (dp4a_uu(P[j], P[j], 0) << 4) | j;
     }
-    uint32_t total = 0;
-    uint64_t idx = 0;
+    // Texels from 15 down to 0, eight per index word: the word is shifted up one nibble per texel
+    // (one IMAD), the subset mask sits with the current texel's bit in the sign position.
+    uint32_t total = 0, word_hi = 0, word_lo = 0;
+    uint32_t m = mask << 16;
+#pragma unroll 1
+    for (int h = 1; h >= 0; h--) {
+        uint32_t acc = 0;
 #pragma unroll 2
-    for (int i = 0; i < 16; i++) {
-        const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
-        int best = 0x7FFFFFFF;
+        for (int i = 8 * h + 7; i >= 8 * h; i--) {
+            const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
+            int best = 0x7FFFFFFF;
 #pragma unroll
-        for (int j = 0; j < L; j += 2)  // two entries per 3-input min (VIMNMX3)
-            best = __vimin3_s32(best, K[j] - (dp4a_uu(p, P[j], 0) << 5), K[j + 1] - (dp4a_uu(p, P[j + 1], 0) << 5));
-        best += dp4a_uu(p, p, 0) << 4;
-        const bool in = (mask >> i) & 1u;
-        total += in ? (uint32_t)(best >> 4) : 0u;
-        idx |= (uint64_t)(in ? (uint32_t)(best & 15) : 0u) << (4 * i);
+            for (int j = 0; j < L; j += 2)  // two entries per 3-input min (VIMNMX3)
+                best = __vimin3_s32(best, K[j] - (dp4a_uu(p, P[j], 0) << 5), K[j + 1] - (dp4a_uu(p, P[j + 1], 0) << 5));
+            best += dp4a_uu(p, p, 0) << 4;
+            const uint32_t in = (uint32_t)((int)m >> 31);  // all ones for a texel of the subset
+            m <<= 1;
+            const uint32_t b = (uint32_t)best & in;
+            total += b >> 4;
+            acc = acc * 16u + (b & 15u);
+        }
+        word_hi = h ? acc : word_hi;
+        word_lo = h ? word_lo : acc;
     }
+    const uint64_t idx = ((uint64_t)word_hi << 32) | word_lo;
     idx_out = idx;
     return total;
 }
