@@ -310,7 +310,7 @@ __device__ __forceinline__ uint32_t weight_bytes(uint32_t nib16) {
 // (LSB forced to p), (2^bits - 1) / 255 without
 __device__ __forceinline__ int quant_pbit(float x, float scale, int maxq, int p) {
     const float y = x * scale;
-    const int q = (int)floorf((y - (float)p) * 0.5f + 0.5f);
+    const int q = (int)floorf(__fmaf_rn(y - (float)p, 0.5f, 0.5f));  // halving is exact: same value as mul, add
     return min(max(q, 0), maxq);
 }
 __device__ __forceinline__ int quant_plain(float x, float scale, int maxq) {
@@ -363,13 +363,17 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
         // ---- p-bits ----
         int ncombo = 1;
         uint32_t combo0 = 0;  // bit e = p-bit of end point e for combination 0
+        bool decided = false;  // end points already quantised by the p-bit decision below
+        uint32_t dq0 = 0, dq1 = 0, de0 = 0, de1 = 0;
         if (pbmode != PB_NONE) {
             if (pb_search) {
                 ncombo = pbmode == PB_PER_EP ? 4 : 2;
             } else {
                 // squared distance of the float end point to its quantised value, for p = 0 and p = 1:
-                // per end point (sums over c), and over both end points in (e, c) order for a shared p-bit
+                // per end point (sums over c), and over both end points in (e, c) order for a shared p-bit.
+                // Both quantisations are kept (bytes per channel), the chosen one is used as it is.
                 float e0s[2] = {0.0f, 0.0f}, e1s[2] = {0.0f, 0.0f}, s0 = 0.0f, s1 = 0.0f;
+                uint32_t qq[2][2] = {{0, 0}, {0, 0}}, ee[2][2] = {{0, 0}, {0, 0}};  // [end point][p]
 #pragma unroll
                 for (int e = 0; e < 2; e++) {
 #pragma unroll
@@ -377,11 +381,17 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
                         if (c < nc) {
                             const float x = e ? P.hi[c] : P.lo[c];
                             int q = quant_pbit(x, scale, maxq, 0);
-                            float d = (float)expand_bits(q << 1, bits + 1) - x;
+                            int ex = expand_bits(q << 1, bits + 1);
+                            float d = (float)ex - x;
                             const float d0 = d * d;
+                            qq[e][0] |= (uint32_t)q << (8 * c);
+                            ee[e][0] |= (uint32_t)ex << (8 * c);
                             q = quant_pbit(x, scale, maxq, 1);
-                            d = (float)expand_bits((q << 1) | 1, bits + 1) - x;
+                            ex = expand_bits((q << 1) | 1, bits + 1);
+                            d = (float)ex - x;
                             const float d1 = d * d;
+                            qq[e][1] |= (uint32_t)q << (8 * c);
+                            ee[e][1] |= (uint32_t)ex << (8 * c);
                             e0s[e] = e0s[e] + d0;
                             e1s[e] = e1s[e] + d1;
                             s0 = s0 + d0;
@@ -393,6 +403,11 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
                     combo0 = (e1s[0] < e0s[0] ? 1u : 0u) | (e1s[1] < e0s[1] ? 2u : 0u);
                 else
                     combo0 = s1 < s0 ? 3u : 0u;
+                decided = true;
+                dq0 = (combo0 & 1u) ? qq[0][1] : qq[0][0];
+                de0 = (combo0 & 1u) ? ee[0][1] : ee[0][0];
+                dq1 = (combo0 & 2u) ? qq[1][1] : qq[1][0];
+                de1 = (combo0 & 2u) ? ee[1][1] : ee[1][0];
             }
         }
 #pragma unroll 1
@@ -400,26 +415,28 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
             uint32_t pb = combo0;
             if (ncombo == 4) pb = (uint32_t)k;  // (k & 1, k >> 1)
             if (ncombo == 2) pb = k ? 3u : 0u;
-            uint32_t q0 = 0, q1 = 0, e0 = 0, e1 = 0;
+            uint32_t q0 = dq0, q1 = dq1, e0 = de0, e1 = de1;
+            if (!decided) {
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
-                int qa, qb, ea, eb;
-                if (pbmode == PB_NONE) {
-                    qa = quant_plain(P.lo[c], scale, maxq);
-                    qb = quant_plain(P.hi[c], scale, maxq);
-                    ea = expand_bits(qa, bits);
-                    eb = expand_bits(qb, bits);
-                } else {
-                    const int pa = pb & 1, pbb = (pb >> 1) & 1;
-                    qa = quant_pbit(P.lo[c], scale, maxq, pa);
-                    qb = quant_pbit(P.hi[c], scale, maxq, pbb);
-                    ea = expand_bits((qa << 1) | pa, bits + 1);
-                    eb = expand_bits((qb << 1) | pbb, bits + 1);
+                for (int c = 0; c < 4; c++) {
+                    int qa, qb, ea, eb;
+                    if (pbmode == PB_NONE) {
+                        qa = quant_plain(P.lo[c], scale, maxq);
+                        qb = quant_plain(P.hi[c], scale, maxq);
+                        ea = expand_bits(qa, bits);
+                        eb = expand_bits(qb, bits);
+                    } else {
+                        const int pa = pb & 1, pbb = (pb >> 1) & 1;
+                        qa = quant_pbit(P.lo[c], scale, maxq, pa);
+                        qb = quant_pbit(P.hi[c], scale, maxq, pbb);
+                        ea = expand_bits((qa << 1) | pa, bits + 1);
+                        eb = expand_bits((qb << 1) | pbb, bits + 1);
+                    }
+                    q0 |= (uint32_t)qa << (8 * c);
+                    q1 |= (uint32_t)qb << (8 * c);
+                    e0 |= (uint32_t)ea << (8 * c);
+                    e1 |= (uint32_t)eb << (8 * c);
                 }
-                q0 |= (uint32_t)qa << (8 * c);
-                q1 |= (uint32_t)qb << (8 * c);
-                e0 |= (uint32_t)ea << (8 * c);
-                e1 |= (uint32_t)eb << (8 * c);
             }
             q0 &= chmask;
             q1 &= chmask;
