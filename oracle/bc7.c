@@ -8,7 +8,7 @@
  * mode / endpoint choices.  What IS fixed by a public document is the block format: the decoder
  * below follows the BC7 (BPTC) specification and is cross-checked bit for
  * bit against Pillow's independent BCn decoder in tests/test_oracle_bc7.py.  The encoder is a
- * scalar statement of the search described in DESIGN.md ("BC7 search, spec v1"): the sm_100a
+ * scalar statement of the search described in DESIGN.md ("BC7 search, spec v2"): the sm_100a
  * kernel implements the same specification independently (thread-per-block, dp4a index search)
  * and is required to match this file's output within 0.1 dB PSNR (and does so bit for bit
  * today because all decisions are made on integer error sums and ordered fp32 arithmetic).
@@ -362,14 +362,18 @@ static void fit_subset(const uint8_t px[16][4], int mask, const fit_cfg* cfg, co
     float mean[4];
     const float rn = 1.0f / (float)n;
     for (int c = 0; c < nc; c++) mean[c] = (float)S1[c] * rn;
-    float tmin = 3.0e38f, tmax = -3.0e38f;
+    /* projections of the raw texels; the mean's projection is taken off the two extremes afterwards */
+    float tmin = 3.0e38f, tmax = -3.0e38f, mv = 0.0f;
+    for (int c = 0; c < nc; c++) mv = fmaf(mean[c], v[c], mv);
     for (int i = 0; i < 16; i++) {
         if (!((mask >> i) & 1)) continue;
         float t = 0.0f;
-        for (int c = 0; c < nc; c++) t = fmaf((float)px[i][c] - mean[c], v[c], t);
+        for (int c = 0; c < nc; c++) t = fmaf((float)px[i][c], v[c], t);
         if (t < tmin) tmin = t;
         if (t > tmax) tmax = t;
     }
+    tmin = tmin - mv;
+    tmax = tmax - mv;
     float lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
     for (int c = 0; c < nc; c++) {
         lo[c] = clampf(fmaf(tmin, v[c], mean[c]), 0.0f, 255.0f);
@@ -409,7 +413,7 @@ static void fit_subset(const uint8_t px[16][4], int mask, const fit_cfg* cfg, co
     }
 }
 
-/* Partition estimator (spec v1 "estimate"): for every subset, error of the best line fit plus
+/* Partition estimator (spec v2 "estimate"): for every subset, error of the best line fit plus
  * the index quantisation term, from integer moments.  Returns A = sum tr/n, B = sum lambda/n. */
 static void subset_line_stats(int n, const int S1[4], const int S2[10], int nc, float* tr_n,
                               float* lam_n) {
