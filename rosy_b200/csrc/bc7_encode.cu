@@ -36,12 +36,28 @@
 namespace rosy_tex {
 namespace {
 
+// unroll factors of the texel loop in evaluate<IB> (8 texels per index word): measured on B200,
+// 2/2/2 3947, 8/4/2 4025, 8/8/2 4113, 8/4/4 4108, 8/8/4 4133, 8/8/8 4014 Mpix/s (less loop and address
+// arithmetic until the code outgrows the instruction cache); the projection loop of prepare: 4 beats 8 and 16
+#ifndef BC7_U2
+#define BC7_U2 8
+#endif
+#ifndef BC7_U3
+#define BC7_U3 8
+#endif
+#ifndef BC7_U4
+#define BC7_U4 4
+#endif
+#ifndef BC7_UP
+#define BC7_UP 4
+#endif
 #ifndef BC7_NT
 #define BC7_NT 512
 #endif
 #ifndef BC7_JOB_SYNC
 #define BC7_JOB_SYNC 0
 #endif
+constexpr int EVAL_U2 = BC7_U2, EVAL_U3 = BC7_U3, EVAL_U4 = BC7_U4, PREP_U = BC7_UP;
 constexpr int NT = BC7_NT;   // threads (= blocks) per CTA
 constexpr int TOPK = 6;   // most partitions refined per mode (high tier)
 constexpr int MAXJOBS = 96;
@@ -221,7 +237,7 @@ __device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, 
     float tmin = 3.0e38f, tmax = -3.0e38f, mv = 0.0f;
 #pragma unroll
     for (int c = 0; c < NC; c++) mv = __fmaf_rn(mean[c], v[c], mv);
-#pragma unroll 4
+#pragma unroll(PREP_U)
     for (int i = 0; i < 16; i++) {
         const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
         float t = 0.0f;
@@ -274,7 +290,7 @@ __device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t 
 #pragma unroll 1
     for (int h = 1; h >= 0; h--) {
         uint32_t acc = 0;
-#pragma unroll 2
+#pragma unroll(IB == 2 ? EVAL_U2 : (IB == 3 ? EVAL_U3 : EVAL_U4))
         for (int i = 8 * h + 7; i >= 8 * h; i--) {
             const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
             int best = 0x7FFFFFFF;
