@@ -7,7 +7,7 @@
  * NVTT 3.2.5 is closed source and absent => PARITY UNPINNED for the encoder's
  * mode / endpoint choices.  What IS fixed by a public document is the block format: the decoder
  * below follows the BC7 (BPTC) specification and is cross-checked bit for
- * bit against Pillow's independent BCn decoder in tests/test_oracle_bc7.py.  The encoder is a
+ * bit against Pillow's independent BCn decoder in tests/test_oracle_golden.py.  The encoder is a
  * scalar statement of the search described in DESIGN.md ("BC7 search, spec v2"): the sm_100a
  * kernel implements the same specification independently (thread-per-block, dp4a index search)
  * and is required to match this file's output within 0.1 dB PSNR (and does so bit for bit
@@ -169,12 +169,21 @@ typedef struct {
     int pb_search;          /* 1: evaluate every p-bit combination, 0: nearest-endpoint p-bits */
 } tier;
 
-/* fast / normal / high  ~  nvtt::Quality_Fastest / Normal / Production */
+/* fast / normal / high  ~  nvtt::Quality_Fastest / Normal / Production.
+ * FROZEN as "spec v2": tests/golden/bc7_spec_v2.npz holds the blocks these three tiers emit and
+ * tests/test_oracle_golden.py fails when this file stops reproducing them.  A change to any decision
+ * below is a new spec version: regenerate the golden file under a new name with the PSNR table of
+ * tools/bc7_quality_gap.py in the commit. */
 static const tier TIERS[3] = {
     {1, 0, 0, 0, 1, 1, 0, 1, 0},
     {3, 2, 0, 0, 2, 4, 1, 2, 0},
     {6, 4, 3, 3, 4, 4, 4, 3, 1},
 };
+/* ORACLE_Q_EXHAUSTIVE (oracle only, never a product tier): no partition ranking at all - every
+ * partition of every partitioned mode, every rotation and index selector, every p-bit combination,
+ * least squares until it stops improving.  An upper bound on what this family of fits can reach,
+ * used as the independent quality ceiling of the three product tiers. */
+static const tier TIER_EXHAUSTIVE = {64, 64, 16, 64, 64, 4, 4, 16, 1};
 
 typedef struct {
     int q[2][4];  /* quantised endpoint fields (without p-bit) */
@@ -541,8 +550,9 @@ typedef struct {
     uint32_t err;
 } solution;
 
-static void try_partitioned(const uint8_t px3[16][4], const uint8_t px4[16][4], int mode,
-                            int partition, const tier* T, solution* best) {
+/* bias: error the mode cannot avoid (alpha of an RGB-only mode on a block with alpha; 0 otherwise) */
+static void try_partitioned_bias(const uint8_t px3[16][4], const uint8_t px4[16][4], int mode,
+                                 int partition, const tier* T, uint32_t bias, solution* best) {
     const mode_info* mi = &MODES[mode];
     fit_cfg cfg = {mi->ab ? 4 : 3, mi->cb, mi->epb ? PB_PER_EP : (mi->spb ? PB_SHARED : PB_NONE),
                    mi->ib};
@@ -551,7 +561,8 @@ static void try_partitioned(const uint8_t px3[16][4], const uint8_t px4[16][4], 
     memset(&s, 0, sizeof s);
     s.mode = mode;
     s.partition = partition;
-    s.err = 0;
+    s.err = bias;
+    if (s.err >= best->err) return;
     for (int k = 0; k < mi->ns; k++) {
         int mask = 0;
         for (int i = 0; i < 16; i++)
@@ -568,6 +579,11 @@ static void try_partitioned(const uint8_t px3[16][4], const uint8_t px4[16][4], 
         if (s.err >= best->err) return; /* cannot win any more */
     }
     if (s.err < best->err) *best = s;
+}
+
+static void try_partitioned(const uint8_t px3[16][4], const uint8_t px4[16][4], int mode,
+                            int partition, const tier* T, solution* best) {
+    try_partitioned_bias(px3, px4, mode, partition, T, 0, best);
 }
 
 static void try_mode45(const uint8_t px4[16][4], int mode, int rotation, int idxsel, const tier* T,
@@ -710,7 +726,8 @@ static void pack_solution(solution* s, uint8_t blk[16]) {
 }
 
 void oracle_bc7_encode_block(const uint8_t rgba[64], int quality, uint8_t blk[16]) {
-    const tier* T = &TIERS[quality < 0 ? 0 : (quality > 2 ? 2 : quality)];
+    const int exhaustive = quality == ORACLE_Q_EXHAUSTIVE;
+    const tier* T = exhaustive ? &TIER_EXHAUSTIVE : &TIERS[quality < 0 ? 0 : (quality > 2 ? 2 : quality)];
     uint8_t px4[16][4], px3[16][4];
     int solid = 1, has_alpha = 0;
     for (int i = 0; i < 16; i++) {
@@ -742,7 +759,15 @@ void oracle_bc7_encode_block(const uint8_t rgba[64], int quality, uint8_t blk[16
     }
     /* mode 6: one subset, RGBA 7.7.7.7 + p-bit per end point, 4-bit indices */
     try_partitioned(px3, px4, 6, 0, T, &best);
-    if (!has_alpha) {
+    if (exhaustive) {
+        uint32_t assd = 0; /* RGB-only modes decode alpha = 255 */
+        for (int i = 0; i < 16; i++) assd += (uint32_t)((255 - px4[i][3]) * (255 - px4[i][3]));
+        for (int p = 0; p < 64; p++) try_partitioned_bias(px3, px4, 1, p, T, assd, &best);
+        for (int p = 0; p < 64; p++) try_partitioned_bias(px3, px4, 3, p, T, assd, &best);
+        for (int p = 0; p < 16; p++) try_partitioned_bias(px3, px4, 0, p, T, assd, &best);
+        for (int p = 0; p < 64; p++) try_partitioned_bias(px3, px4, 2, p, T, assd, &best);
+        for (int p = 0; p < 64; p++) try_partitioned(px3, px4, 7, p, T, &best);
+    } else if (!has_alpha) {
         if (T->n1 || T->n3) {
             toplist l1, l3;
             estimate_partitions(px4, 2, 64, 3, 3, &l1, 2, &l3);

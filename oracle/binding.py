@@ -10,6 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 KIND_SRGB, KIND_NORMAL = 0, 1
 FMT_BC7, FMT_BC5, FMT_BC4 = 0, 1, 2
 Q_FAST, Q_NORMAL, Q_HIGH = 0, 1, 2
+Q_EXHAUSTIVE = 3  # oracle-only quality ceiling (every partition / rotation / p-bit, LS to convergence)
 NORMALIZE_OFF, NORMALIZE_UNPACK = 0, 1
 DDS_HEADER_BYTES = 148
 

@@ -32,6 +32,9 @@ enum { ORACLE_FMT_BC7 = 0, ORACLE_FMT_BC5 = 1, ORACLE_FMT_BC4 = 2 };
 /* Quality tiers: nvtt::Quality_Fastest / Normal / Production (reference uses Normal only,
  * Packager.cpp:277 and NVTT default at :228-229). */
 enum { ORACLE_Q_FAST = 0, ORACLE_Q_NORMAL = 1, ORACLE_Q_HIGH = 2 };
+/* Oracle-only ceiling: every partition / rotation / index selector / p-bit combination, least
+ * squares to convergence.  Not a product tier; it bounds what the three tiers above can reach. */
+enum { ORACLE_Q_EXHAUSTIVE = 3 };
 /* normalizeNormalMap reading: 1 = unpack 2v-1, safe-normalise, repack (default);
  * 0 = literal NVTT-2 no-op (surface was never flagged setNormalMap(true)). */
 enum { ORACLE_NORMALIZE_OFF = 0, ORACLE_NORMALIZE_UNPACK = 1 };

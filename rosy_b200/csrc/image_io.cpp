@@ -233,36 +233,105 @@ static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     return ROSY_TEX_OK;
 }
 
-// ---------------------------------------------------------------- TGA (types 2, 3, 10, 11; 8/24/32 bpp)
+// ---------------------------------------------------------------- TGA
+// Types 1/9 (colour-mapped), 2/10 (true colour), 3/11 (grey), raw or RLE; 8/15/16/24/32 bits per pixel
+// or per palette entry, 8- or 16-bit palette indices.  Behaviour follows the reference tree's
+// stb_image.h:5735-6074 so decoded bytes are identical (tests/golden/stb_image_tga.npz): 15/16-bit
+// pixels are 5-5-5 expanded with (v*255)/31 and carry no alpha, 16-bit grey is grey + alpha, the
+// right-to-left descriptor bit is ignored, `first entry index` of a colour map is a byte skip, and an
+// out-of-range palette index reads entry 0.  Unlike stb, truncated files are an error.
 static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H) {
     if (f.size() < 18) return ROSY_TEX_ERR_DECODE;
-    const int idlen = f[0], cmap = f[1], type = f[2];
+    const int idlen = f[0], cmap = f[1];
+    int type = f[2];
+    const size_t pal_start = f[3] | (f[4] << 8), pal_len = f[5] | (f[6] << 8);
+    const int pal_bits = f[7];
     const uint32_t w = f[12] | (f[13] << 8), h = f[14] | (f[15] << 8);
     const int bpp = f[16], desc = f[17];
-    if (cmap != 0 || !(type == 2 || type == 3 || type == 10 || type == 11)) return ROSY_TEX_ERR_DECODE;
-    const bool grey = type == 3 || type == 11, rle = type >= 10;
-    if (!((grey && bpp == 8) || (!grey && (bpp == 24 || bpp == 32))) || w == 0 || h == 0) return ROSY_TEX_ERR_DECODE;
-    const size_t bytes = (size_t)bpp / 8, n = (size_t)w * h;
-    std::vector<uint8_t> px(n * bytes);
+    if (cmap > 1 || w == 0 || h == 0 || w > 32768 || h > 32768) return ROSY_TEX_ERR_DECODE;
+    if (cmap ? !(type == 1 || type == 9) : !(type == 2 || type == 3 || type == 10 || type == 11))
+        return ROSY_TEX_ERR_DECODE;
+    const bool rle = type >= 8;
+    if (rle) type -= 8;
+    if (cmap && bpp != 8 && bpp != 16) return ROSY_TEX_ERR_DECODE;
+    // components of a pixel (or palette entry): 1 grey, 2 grey + alpha, 3 RGB (also 5-5-5), 4 RGBA
+    const int cbits = cmap ? pal_bits : bpp;
+    int comp = 0;
+    bool rgb16 = false;
+    switch (cbits) {
+        case 8: comp = 1; break;
+        case 16:
+            if (!cmap && type == 3) {
+                comp = 2;
+                break;
+            }
+            [[fallthrough]];
+        case 15:
+            comp = 3;
+            rgb16 = true;
+            break;
+        case 24: comp = 3; break;
+        case 32: comp = 4; break;
+        default: return ROSY_TEX_ERR_DECODE;
+    }
+    const size_t n = (size_t)w * h;
+    const size_t src_bytes = cmap ? (size_t)bpp / 8 : (rgb16 ? 2 : (size_t)comp);  // per pixel in the file
     size_t pos = 18 + (size_t)idlen;
+    if (pos > f.size()) return ROSY_TEX_ERR_DECODE;
+    // palette
+    std::vector<uint8_t> pal;
+    auto rgb555 = [](const uint8_t* s, uint8_t* o) {
+        const uint32_t px = s[0] | (s[1] << 8);
+        o[0] = (uint8_t)((((px >> 10) & 31u) * 255u) / 31u);
+        o[1] = (uint8_t)((((px >> 5) & 31u) * 255u) / 31u);
+        o[2] = (uint8_t)(((px & 31u) * 255u) / 31u);
+    };
+    if (cmap) {
+        if (pal_len == 0) return ROSY_TEX_ERR_DECODE;
+        pos += pal_start;
+        const size_t eb = rgb16 ? 2 : (size_t)comp;
+        if (pos > f.size() || pal_len * eb > f.size() - pos) return ROSY_TEX_ERR_DECODE;
+        pal.resize(pal_len * comp);
+        if (rgb16)
+            for (size_t i = 0; i < pal_len; i++) rgb555(&f[pos + 2 * i], &pal[3 * i]);
+        else
+            memcpy(pal.data(), &f[pos], pal_len * comp);
+        pos += pal_len * eb;
+    }
+    // the payload must be able to hold the image before anything of its size is allocated
+    const size_t avail = f.size() - pos;
+    if (rle ? n > avail * 128 : n > avail / src_bytes) return ROSY_TEX_ERR_DECODE;
+    std::vector<uint8_t> px(n * comp);
+    auto read_pixel = [&](const uint8_t* s, uint8_t* o) {
+        if (cmap) {
+            size_t idx = bpp == 8 ? s[0] : (size_t)(s[0] | (s[1] << 8));
+            if (idx >= pal_len) idx = 0;
+            memcpy(o, &pal[idx * comp], (size_t)comp);
+        } else if (rgb16) {
+            rgb555(s, o);
+        } else {
+            memcpy(o, s, (size_t)comp);
+        }
+    };
     if (!rle) {
-        if (pos + n * bytes > f.size()) return ROSY_TEX_ERR_DECODE;
-        memcpy(px.data(), &f[pos], n * bytes);
+        for (size_t i = 0; i < n; i++) read_pixel(&f[pos + i * src_bytes], &px[i * comp]);
     } else {
         size_t o = 0;
         while (o < n) {
             if (pos >= f.size()) return ROSY_TEX_ERR_DECODE;
             const int hd = f[pos++];
-            const size_t cnt = (size_t)(hd & 127) + 1;
-            if (o + cnt > n) return ROSY_TEX_ERR_DECODE;
+            size_t cnt = (size_t)(hd & 127) + 1;
+            if (cnt > n - o) cnt = n - o;  // a packet may run past the last pixel (stb stops there too)
             if (hd & 128) {
-                if (pos + bytes > f.size()) return ROSY_TEX_ERR_DECODE;
-                for (size_t k = 0; k < cnt; k++) memcpy(&px[(o + k) * bytes], &f[pos], bytes);
-                pos += bytes;
+                if (src_bytes > f.size() - pos) return ROSY_TEX_ERR_DECODE;
+                uint8_t one[4];
+                read_pixel(&f[pos], one);
+                for (size_t k = 0; k < cnt; k++) memcpy(&px[(o + k) * comp], one, (size_t)comp);
+                pos += src_bytes;
             } else {
-                if (pos + cnt * bytes > f.size()) return ROSY_TEX_ERR_DECODE;
-                memcpy(&px[o * bytes], &f[pos], cnt * bytes);
-                pos += cnt * bytes;
+                if (cnt * src_bytes > f.size() - pos) return ROSY_TEX_ERR_DECODE;
+                for (size_t k = 0; k < cnt; k++) read_pixel(&f[pos + k * src_bytes], &px[(o + k) * comp]);
+                pos += cnt * src_bytes;
             }
             o += cnt;
         }
@@ -270,22 +339,24 @@ static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     W = w;
     H = h;
     rgba.resize(n * 4);
-    const bool top = desc & 0x20, right = desc & 0x10;
-    for (uint32_t y = 0; y < h; y++)
-        for (uint32_t x = 0; x < w; x++) {
-            const size_t sy = top ? y : h - 1 - y, sx = right ? w - 1 - x : x;
-            const uint8_t* s = &px[(sy * w + sx) * bytes];
-            uint8_t* o = &rgba[((size_t)y * w + x) * 4];
-            if (grey) {
+    const bool top = desc & 0x20;
+    const bool swap_rb = comp >= 3 && !rgb16;  // stored BGR(A); 5-5-5 pixels were expanded in RGB order
+    for (uint32_t y = 0; y < h; y++) {
+        const size_t sy = top ? y : h - 1 - y;
+        const uint8_t* s = &px[sy * w * comp];
+        uint8_t* o = &rgba[(size_t)y * w * 4];
+        for (uint32_t x = 0; x < w; x++, s += comp, o += 4) {
+            if (comp <= 2) {
                 o[0] = o[1] = o[2] = s[0];
-                o[3] = 255;
+                o[3] = comp == 2 ? s[1] : 255;
             } else {
-                o[0] = s[2];
+                o[0] = swap_rb ? s[2] : s[0];
                 o[1] = s[1];
-                o[2] = s[0];
-                o[3] = bytes == 4 ? s[3] : 255;
+                o[2] = swap_rb ? s[0] : s[2];
+                o[3] = comp == 4 ? s[3] : 255;
             }
         }
+    }
     return ROSY_TEX_OK;
 }
 
@@ -312,8 +383,9 @@ static int decode_pnm(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     }
     pos++;  // single whitespace after maxval
     const int ch = f[1] == '6' ? 3 : 1;
+    if (vals[0] == 0 || vals[1] == 0 || vals[0] > 32768 || vals[1] > 32768 || pos > f.size()) return ROSY_TEX_ERR_DECODE;
     const size_t n = (size_t)vals[0] * vals[1];
-    if (vals[2] != 255 || n == 0 || pos + n * ch > f.size()) return ROSY_TEX_ERR_DECODE;
+    if (vals[2] != 255 || n > (f.size() - pos) / (size_t)ch) return ROSY_TEX_ERR_DECODE;
     W = vals[0];
     H = vals[1];
     rgba.resize(n * 4);

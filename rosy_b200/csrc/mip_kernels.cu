@@ -209,6 +209,7 @@ constexpr int SRGB_BASE = (int)(SRGB_LO >> SRGB_SHIFT);
 constexpr int SRGB_ENTRIES = (int)((SRGB_HI - SRGB_LO) >> SRGB_SHIFT) + 1;
 
 __constant__ float2 c_SRGB_ENCODE[SRGB_ENTRIES];
+__constant__ volatile unsigned int* c_LAYOUT_FAULT;  // mapped host memory, set by a fused launch that found an unexpected shared window
 __constant__ float c_UNORM8[256];  // i / 255.0f, as nvtt::Surface::load produces it
 
 // One texture of a launch.  Lives in kernel parameter space (single texture) or in global memory
@@ -291,6 +292,9 @@ __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map,
         "%3}], [%4];" ::"r"(smem_u32(dst)),
         "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
         : "memory");
+}
+__device__ __forceinline__ void tensormap_acquire(const CUtensorMap* map) {
+    asm volatile("fence.proxy.tensormap::generic.acquire.sys [%0], 128;" ::"l"(map) : "memory");
 }
 // The sRGB->linear table and the alpha table share one array of 256-byte rows, one row per 8-bit
 // value: floats 0..31 hold (lin(v) + SRGB_BIAS) / 4 replicated across the 32 banks (conflict-free
@@ -524,7 +528,14 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     const int grp = threadIdx.x >= NTHREADS_TOTAL ? 1 : 0;
     const int tid = (int)threadIdx.x - grp * NTHREADS_TOTAL, lane = tid & 31, warp = tid >> 5;
     const uint32_t win = smem_u32(smem_raw);
-    if ((win & 0xFFFFu) != SMEM_WINDOW_BASE) __trap();  // the layout below relies on it
+    if ((win & 0xFFFFu) != SMEM_WINDOW_BASE) {
+        // The layout below relies on the window base.  The host probes it per device (fused_window_ok) and
+        // takes the per-level kernels when it differs, so this is never reached in practice; if it is, the
+        // launch does nothing and says so through a flag in mapped host memory - never a trap, which would
+        // poison the context for every other texture in flight.
+        if (threadIdx.x == 0 && blockIdx.x == 0 && c_LAYOUT_FAULT) *c_LAYOUT_FAULT = 1u;
+        return;
+    }
     uint8_t* const lin_raw = smem_raw + (0x10000 - SMEM_WINDOW_BASE);
     GroupSmem& S = *reinterpret_cast<GroupSmem*>(grp ? lin_raw + LIN_BYTES : smem_raw);
     float* const lin_tab = reinterpret_cast<float*>(lin_raw);
@@ -585,6 +596,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             if (want != cur) {
                 cur = want;
                 T = texs ? texs + cur : &single;
+                // the host rewrites the descriptor array for every batch at the same addresses: make the
+                // generic-proxy writes visible to the tensormap proxy before the first copy through this map
+                if (texs) tensormap_acquire(&T->tmap);
                 t_base = T->tile_base;
                 t_tiles_x = T->tiles_x;
                 t_normalize = T->normalize;
@@ -890,8 +904,27 @@ encode_tiled_fn get_encode_tiled() {
     return fn;
 }
 
+// Where the dynamic shared memory of a CTA starts inside its shared window (per device; the fused kernel's
+// table layout needs SMEM_WINDOW_BASE).  Probed with a kernel of the same dynamic size in this module.
+__global__ void smem_window_probe(unsigned int* out) {
+    extern __shared__ __align__(1024) uint8_t probe_raw[];
+    if (threadIdx.x == 0) *out = smem_u32(probe_raw);
+}
+struct DeviceMipState {
+    int window_ok = -1;                 // -1 unknown, 0 generic path only, 1 fused path usable
+    unsigned int* fault_host = nullptr; // mapped; non-zero after a fused launch that refused to run
+};
+DeviceMipState g_dev[64];
+std::mutex g_dev_mu;
+
+bool fused_window_ok() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return g_dev[dev & 63].window_ok == 1;
+}
+
 bool fused_ok(const Chain& c) {
-    return c.lv[0].w % TILE == 0 && c.lv[0].h % TILE == 0 && c.levels >= 7;
+    return c.lv[0].w % TILE == 0 && c.lv[0].h % TILE == 0 && c.levels >= 7 && fused_window_ok();
 }
 
 size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -959,6 +992,14 @@ cudaError_t launch_fused(const MipTex* single, const MipTex* d_texs, const int* 
 
 }  // namespace
 
+// true once a fused launch on the current device has refused to run (unexpected shared-window layout)
+bool mips_layout_fault() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const DeviceMipState& D = g_dev[dev & 63];
+    return D.fault_host && *static_cast<volatile unsigned int*>(D.fault_host) != 0u;
+}
+
 size_t mips_scratch_bytes(const Chain& c) {
     // generic: fp32 level 1 + fp32 level 2 (ping-pong);  fused: ticket + tile tops + two tail buffers
     const size_t l1 = c.levels > 1 ? (size_t)c.lv[1].w * c.lv[1].h * sizeof(float4) : 0;
@@ -969,7 +1010,11 @@ size_t mips_scratch_bytes(const Chain& c) {
     return align256(generic > fused ? generic : fused);
 }
 
-size_t mips_batch_desc_bytes(int n) { return align256((size_t)n * sizeof(MipTex)) + align256((size_t)(n + 1) * sizeof(int)); }
+// two kinds (colour, normal) may be present: each has its own descriptor array and tile-base array, each
+// 256-byte aligned, so the worst case carries one extra alignment gap per array and two extra ints
+size_t mips_batch_desc_bytes(int n) {
+    return align256((size_t)n * sizeof(MipTex)) + 256 + align256((size_t)(n + 2) * sizeof(int)) + 256;
+}
 
 int mips_upload_tables() {
     float lut[256], unorm[256];
@@ -1007,6 +1052,35 @@ int mips_upload_tables() {
         worst = fmax(worst, 0.5 * (hi - lo));
     }
     if (worst > 0.01) return -1;  // table must stay far inside the 1 LSB bar
+    {   // shared-window probe and the fault flag of this device
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> g(g_dev_mu);
+        DeviceMipState& D = g_dev[dev & 63];
+        if (D.window_ok < 0) {
+            D.window_ok = 0;
+            unsigned int* d_out = nullptr;
+            unsigned int base = 0xFFFFFFFFu;
+            if (cudaFuncSetAttribute(smem_window_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM_BYTES) == cudaSuccess &&
+                cudaMalloc(&d_out, 4) == cudaSuccess) {
+                smem_window_probe<<<1, 32, FUSED_SMEM_BYTES>>>(d_out);
+                if (cudaMemcpy(&base, d_out, 4, cudaMemcpyDeviceToHost) == cudaSuccess && (base & 0xFFFFu) == SMEM_WINDOW_BASE)
+                    D.window_ok = 1;
+            }
+            cudaFree(d_out);
+            cudaGetLastError();
+            if (const char* e = getenv("ROSY_TEX_FAKE_WINDOW_MISMATCH"))  // test hook: behave as on a driver with another layout
+                if (atoi(e)) D.window_ok = 0;
+            if (cudaHostAlloc(&D.fault_host, 4, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+                *D.fault_host = 0u;
+                unsigned int* d_flag = nullptr;
+                if (cudaHostGetDevicePointer(&d_flag, D.fault_host, 0) == cudaSuccess)
+                    cudaMemcpyToSymbol(c_LAYOUT_FAULT, &d_flag, sizeof d_flag);
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
     return cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
                    cudaMemcpyToSymbol(c_UNORM8, unorm, sizeof unorm) == cudaSuccess &&
                    cudaMemcpyToSymbol(c_SRGB_ENCODE, enc, sizeof enc) == cudaSuccess

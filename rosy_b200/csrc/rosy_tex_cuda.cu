@@ -13,13 +13,28 @@
 #include <condition_variable>
 #include <deque>
 #include <mutex>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <thread>
 #include <vector>
 
 #include "tex_internal.h"
 
+#include <nvtx3/nvToolsExt.h>
+
 namespace rosy_tex {
+
+// One NVTX range per texture (or per batch of small textures) on the worker thread: lets a timeline show
+// copy / kernel overlap per slot.  Costs nothing when no tool is attached.
+struct NvtxRange {
+    NvtxRange(const char* what, uint32_t w, uint32_t h, int count) {
+        char name[96];
+        snprintf(name, sizeof name, "%s %ux%u x%d", what, w, h, count);
+        nvtxRangePushA(name);
+    }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 int load_image(const char* path, std::vector<uint8_t>& rgba, uint32_t& w, uint32_t& h, std::string& err);
 int mips_upload_tables();
@@ -36,6 +51,20 @@ int fail(int status, const std::string& msg) {
 int cuda_fail(cudaError_t e, const char* what) {
     return fail(ROSY_TEX_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }
+// No exception may cross the C ABI or escape a worker thread (std::bad_alloc from a std::vector sized by a
+// hostile image header would otherwise reach std::terminate through a bare std::thread).
+template <class F>
+int guarded(F&& f) {
+    try {
+        return f();
+    } catch (const std::bad_alloc&) {
+        return fail(ROSY_TEX_ERR_NOMEM, "out of host memory");
+    } catch (const std::exception& e) {
+        return fail(ROSY_TEX_ERR_NOMEM, std::string("internal error: ") + e.what());
+    } catch (...) {
+        return fail(ROSY_TEX_ERR_NOMEM, "internal error");
+    }
+}
 #define CU_TRY(call)                                          \
     do {                                                      \
         cudaError_t e_ = (call);                              \
@@ -49,6 +78,7 @@ struct Slot {
     uint8_t *d_in = nullptr, *d_chain = nullptr, *d_scratch = nullptr, *d_blocks = nullptr, *d_desc = nullptr;
     size_t cap_in = 0, cap_chain = 0, cap_scratch = 0, cap_blocks = 0, cap_desc = 0;
     bool busy = false;
+    bool ticket_dirty = false;  // a pass on this slot failed after its launches: the fused mip kernel's ticket may be non-zero
 };
 
 // A texture for the device workers: host pixels in, DDS bytes out.
@@ -62,6 +92,7 @@ struct Job {
     bool from_file = false;
     std::string dds_path;
     size_t staged = 0;  // pinned bytes this job holds
+    int attempts = 0;   // times the job went back to the queue after a device fault
 };
 
 // Host-side stage of a file job, run by the I/O threads: decode before the device, write after it.
@@ -92,6 +123,8 @@ struct State {
     std::vector<std::thread> workers;
     bool queue_batching = true;  // ROSY_TEX_QUEUE_BATCH=0: one texture per pass whatever its size
     int running = 0;
+    int live_workers = 0;  // device workers that have not retired after a device fault
+    int requeued = 0;      // textures handed to another worker after a device fault (diagnostic)
     int pending = 0;  // submitted textures that are not completely done (decode, device, write)
     // file pipeline: decode / write threads, decoded images waiting for a device slot, pinned staging pool
     std::deque<IoTask> io_queue;
@@ -329,7 +362,13 @@ void release_slot(Slot* sl) {
 enum What { WHAT_DDS, WHAT_MIPS, WHAT_LEVEL };
 
 // host buffers in, host buffers out, on one slot
+int run_host_impl(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len);
 int run_host(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len) {
+    const int rc = run_host_impl(sl, r, what, rgba, out, cap, len);
+    if (rc && rc != ROSY_TEX_ERR_ARG) sl->ticket_dirty = true;
+    return rc;
+}
+int run_host_impl(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len) {
     Chain c = make_chain(r.w, r.h);
     if (what == WHAT_LEVEL) {  // a single level, no mip chain
         c.levels = 1;
@@ -347,9 +386,10 @@ int run_host(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_
     if ((rc = grow(sl->d_chain, sl->cap_chain, chain_bytes))) return rc;
     if ((rc = grow(sl->d_blocks, sl->cap_blocks, blk_bytes))) return rc;
     const size_t sc = mips_scratch_bytes(c);
-    if (sc > sl->cap_scratch) {
+    if (sc > sl->cap_scratch || sl->ticket_dirty) {
         if ((rc = grow(sl->d_scratch, sl->cap_scratch, sc))) return rc;
         CU_TRY(cudaMemsetAsync(sl->d_scratch, 0, 256, sl->stream));  // the fused kernel's ticket
+        sl->ticket_dirty = false;
     }
     CU_TRY(cudaMemcpyAsync(sl->d_in, rgba, in_bytes, cudaMemcpyHostToDevice, sl->stream));
     if (what == WHAT_LEVEL) {
@@ -376,6 +416,7 @@ int run_host(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_
         CU_TRY(cudaMemcpyAsync(out + ROSY_TEX_DDS_HEADER_BYTES, sl->d_blocks, blk_bytes, cudaMemcpyDeviceToHost, sl->stream));
     }
     CU_TRY(cudaStreamSynchronize(sl->stream));
+    if (mips_layout_fault()) return fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
     return ROSY_TEX_OK;
 }
 
@@ -489,8 +530,11 @@ int run_host_batch(Slot* sl, std::vector<HostJob>& jobs) {
         write_dds_header(rs[i], mi[i].chain.levels, jobs[(size_t)i].out);
         CU_TRY(cudaMemcpyAsync(jobs[(size_t)i].out + ROSY_TEX_DDS_HEADER_BYTES, d_blk[i], blk_bytes[i], cudaMemcpyDeviceToHost, sl->stream));
     }
+    sl->ticket_dirty = true;  // until the batch is known to have run to its end
     CU_TRY(cudaStreamSynchronize(sl->stream));
+    if (mips_layout_fault()) return fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
     // the single-texture path relies on a zero ticket at the start of d_scratch: still true (tickets return to zero)
+    sl->ticket_dirty = false;
     return ROSY_TEX_OK;
 }
 
@@ -502,7 +546,7 @@ int run_host_any(const rosy_tex_desc* desc, What what, const uint8_t* rgba, void
     int prev = 0;
     cudaGetDevice(&prev);
     Slot* sl = acquire_slot();
-    rc = run_host(sl, r, what, rgba, static_cast<uint8_t*>(out), cap, len);
+    rc = guarded([&] { return run_host(sl, r, what, rgba, static_cast<uint8_t*>(out), cap, len); });
     release_slot(sl);
     cudaSetDevice(prev);
     return rc;
@@ -580,24 +624,37 @@ constexpr uint64_t BATCH_MEMBER_PX = 1u << 18, BATCH_TOTAL_PX = 4u << 20;
 constexpr size_t BATCH_MAX = 64;
 inline uint64_t job_px(const Job& j) { return (uint64_t)j.desc.width * j.desc.height; }
 
-void worker_main(Slot* sl) {
+// Pop order: largest texture first, so that the long jobs start early and the small ones fill
+// the gaps at the end (LPT).  Small textures are then taken together as described above.
+// Failure handling: a device-level failure (ROSY_TEX_ERR_CUDA / _NOMEM on the device) retires the
+// worker that saw it; its textures go back to the queue once and are finished by the remaining workers
+// (other slots / other devices).  When no worker is left, or a texture fails twice, the error is reported
+// by wait_all, which is the reference's behaviour: any failure aborts the asset (Gltf.cpp:225-229).
+void worker_main(Slot* sl, int slot_index) {
     State& s = st();
     std::vector<Job> jobs;
     std::vector<HostJob> hj;
     std::vector<size_t> lens;
     std::vector<int> rcs;
+    int fault_left = 0;  // test hook: ROSY_TEX_FAULT_SLOT=<slot index> makes that worker's first pass fail like a lost device
+    if (const char* e = getenv("ROSY_TEX_FAULT_SLOT")) fault_left = atoi(e) == slot_index ? 1 : 0;
     for (;;) {
         jobs.clear();
         {
             std::unique_lock<std::mutex> g(s.mu);
             s.cv.wait(g, [&] { return s.stop || !s.queue.empty(); });
             if (s.stop && s.queue.empty()) return;
-            const size_t share = (s.queue.size() + s.workers.size() - 1) / (s.workers.empty() ? 1 : s.workers.size());
-            jobs.push_back(std::move(s.queue.front()));
-            s.queue.pop_front();
+            const size_t live = s.live_workers > 0 ? (size_t)s.live_workers : 1;
+            const size_t share = (s.queue.size() + live - 1) / live;
+            size_t big = 0;
+            for (size_t i = 1; i < s.queue.size(); i++)
+                if (job_px(s.queue[i]) > job_px(s.queue[big])) big = i;
+            jobs.push_back(std::move(s.queue[big]));
+            s.queue.erase(s.queue.begin() + (long)big);
             uint64_t px = job_px(jobs[0]);
+            // the largest one is small: so is everything else in the queue
             if (s.queue_batching && px <= BATCH_MEMBER_PX)
-                while (!s.queue.empty() && jobs.size() < share && jobs.size() < BATCH_MAX && job_px(s.queue.front()) <= BATCH_MEMBER_PX &&
+                while (!s.queue.empty() && jobs.size() < share && jobs.size() < BATCH_MAX &&
                        px + job_px(s.queue.front()) <= BATCH_TOTAL_PX) {
                     px += job_px(s.queue.front());
                     jobs.push_back(std::move(s.queue.front()));
@@ -609,38 +666,64 @@ void worker_main(Slot* sl) {
         lens.assign(n, 0);
         rcs.assign(n, 0);
         bool batched = false;
-        if (n > 1) {
-            hj.resize(n);
-            int rc = 0;
-            for (size_t i = 0; i < n && !rc; i++) {
-                rc = resolve(&jobs[i].desc, hj[i].r);
-                hj[i].rgba = jobs[i].rgba;
-                hj[i].out = static_cast<uint8_t*>(jobs[i].out);
-                hj[i].cap = jobs[i].cap;
-                hj[i].len = jobs[i].len ? jobs[i].len : &lens[i];
+        const int guard_rc = guarded([&] {
+            if (fault_left > 0) {
+                fault_left--;
+                for (size_t i = 0; i < n; i++) rcs[i] = fail(ROSY_TEX_ERR_CUDA, "injected device fault (ROSY_TEX_FAULT_SLOT)");
+                return (int)ROSY_TEX_OK;
             }
-            if (!rc) rc = run_host_batch(sl, hj);
-            batched = rc == 0;  // a failing member: one by one below, so that the error lands on that texture alone
-        }
-        if (!batched)
-            for (size_t i = 0; i < n; i++) {
-                Resolved r;
-                rcs[i] = resolve(&jobs[i].desc, r);
-                if (!rcs[i])
-                    rcs[i] = run_host(sl, r, WHAT_DDS, jobs[i].rgba, static_cast<uint8_t*>(jobs[i].out), jobs[i].cap,
-                                      jobs[i].len ? jobs[i].len : &lens[i]);
-                if (rcs[i] && n > 1) {  // keep the message of the first failing member
-                    std::lock_guard<std::mutex> g(s.mu);
-                    note_error_locked(s, rcs[i]);
+            NvtxRange range(n > 1 ? "rosy_tex batch" : "rosy_tex texture", jobs[0].desc.width, jobs[0].desc.height, (int)n);
+            if (n > 1) {
+                hj.resize(n);
+                int rc = 0;
+                for (size_t i = 0; i < n && !rc; i++) {
+                    rc = resolve(&jobs[i].desc, hj[i].r);
+                    hj[i].rgba = jobs[i].rgba;
+                    hj[i].out = static_cast<uint8_t*>(jobs[i].out);
+                    hj[i].cap = jobs[i].cap;
+                    hj[i].len = jobs[i].len ? jobs[i].len : &lens[i];
                 }
+                if (!rc) rc = run_host_batch(sl, hj);
+                batched = rc == 0;  // a failing member: one by one below, so that the error lands on that texture alone
             }
+            if (!batched)
+                for (size_t i = 0; i < n; i++) {
+                    Resolved r;
+                    rcs[i] = resolve(&jobs[i].desc, r);
+                    if (!rcs[i])
+                        rcs[i] = run_host(sl, r, WHAT_DDS, jobs[i].rgba, static_cast<uint8_t*>(jobs[i].out), jobs[i].cap,
+                                          jobs[i].len ? jobs[i].len : &lens[i]);
+                    if (rcs[i] && n > 1) {  // keep the message of the first failing member
+                        std::lock_guard<std::mutex> g(s.mu);
+                        note_error_locked(s, rcs[i]);
+                    }
+                }
+            return (int)ROSY_TEX_OK;
+        });
+        if (guard_rc)
+            for (size_t i = 0; i < n; i++) rcs[i] = rcs[i] ? rcs[i] : guard_rc;
+        bool retire = false;
         {
             std::lock_guard<std::mutex> g(s.mu);
+            // a device-level failure: hand the textures to the other workers (once per texture) and retire
+            bool device_fault = false;
+            for (size_t i = 0; i < n; i++) device_fault = device_fault || rcs[i] == ROSY_TEX_ERR_CUDA;
+            if (device_fault && s.live_workers > 1) {
+                retire = true;
+                s.live_workers--;
+                cudaGetLastError();
+            }
             for (size_t i = 0; i < n; i++) {
                 Job& job = jobs[i];
-                const int rc = rcs[i];
-                note_error_locked(s, rc);
+                int rc = rcs[i];
                 s.running--;
+                if (retire && rc == ROSY_TEX_ERR_CUDA && job.attempts == 0) {
+                    job.attempts++;
+                    s.requeued++;
+                    s.queue.push_back(std::move(job));
+                    continue;
+                }
+                note_error_locked(s, rc);
                 if (job.from_file) {
                     s.decoded_inflight--;
                     if (rc) {
@@ -664,6 +747,7 @@ void worker_main(Slot* sl) {
             }
         }
         s.cv.notify_all();
+        if (retire) return;
     }
 }
 
@@ -680,7 +764,8 @@ void start_workers_locked(State& s) {
         cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking);
         s.slots.push_back(sl);
     }
-    for (size_t i = 0; i < n; i++) s.workers.emplace_back(worker_main, &s.slots[n + i]);
+    s.live_workers = (int)n;
+    for (size_t i = 0; i < n; i++) s.workers.emplace_back(worker_main, &s.slots[n + i], (int)i);
 }
 
 int write_dds_file(const std::string& dds_path, const void* data, size_t len) {
@@ -729,8 +814,10 @@ void io_main() {
             std::vector<uint8_t> rgba;
             uint32_t w = 0, h = 0;
             std::string err;
-            int rc = load_image(t.path.c_str(), rgba, w, h, err);
-            if (rc) fail(rc, err);
+            int rc = guarded([&] {
+                const int r = load_image(t.path.c_str(), rgba, w, h, err);
+                return r ? fail(r, err) : r;
+            });
             Job j;
             j.desc = {w, h, t.kind, -1, -1, -1};
             Resolved r;
@@ -868,6 +955,7 @@ void rosy_tex_shutdown(void) {
     for (std::thread& t : s.io_workers) t.join();
     std::lock_guard<std::mutex> g(s.mu);
     s.workers.clear();
+    s.live_workers = 0;
     s.io_workers.clear();
     s.io_queue.clear();
     for (PinBuf& b : s.pinned) cudaFreeHost(b.p);
@@ -920,7 +1008,7 @@ int rosy_tex_generate_texture_file(const char* image_path, int kind, const char*
     int prev = 0;
     cudaGetDevice(&prev);
     Slot* sl = acquire_slot();
-    rc = run_file(sl, image_path, kind, dds_path ? dds_path : "");
+    rc = guarded([&] { return run_file(sl, image_path, kind, dds_path ? dds_path : ""); });
     release_slot(sl);
     cudaSetDevice(prev);
     return rc;
@@ -936,14 +1024,16 @@ int rosy_tex_generate_normal_map_texture(const char* image_path) {
 
 int rosy_tex_load_image(const char* image_path, uint8_t** rgba, uint32_t* width, uint32_t* height) {
     if (!image_path || !rgba || !width || !height) return fail(ROSY_TEX_ERR_ARG, "null argument");
-    std::vector<uint8_t> px;
-    std::string err;
-    int rc = load_image(image_path, px, *width, *height, err);
-    if (rc) return fail(rc, err);
-    *rgba = static_cast<uint8_t*>(malloc(px.size()));
-    if (!*rgba) return fail(ROSY_TEX_ERR_NOMEM, "malloc");
-    memcpy(*rgba, px.data(), px.size());
-    return ROSY_TEX_OK;
+    return guarded([&] {
+        std::vector<uint8_t> px;
+        std::string err;
+        int rc = load_image(image_path, px, *width, *height, err);
+        if (rc) return fail(rc, err);
+        *rgba = static_cast<uint8_t*>(malloc(px.size()));
+        if (!*rgba) return fail(ROSY_TEX_ERR_NOMEM, "malloc");
+        memcpy(*rgba, px.data(), px.size());
+        return (int)ROSY_TEX_OK;
+    });
 }
 
 void rosy_tex_free_image(uint8_t* rgba) { free(rgba); }
@@ -997,7 +1087,7 @@ int rosy_tex_compress_level_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba
 int rosy_tex_submit(const char* image_path, int kind) {
     if (!image_path) return fail(ROSY_TEX_ERR_ARG, "null path");
     if (kind < 0 || kind > 3) return fail(ROSY_TEX_ERR_ARG, "bad kind");
-    return enqueue_file(image_path, kind);
+    return guarded([&] { return enqueue_file(image_path, kind); });
 }
 
 int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* out, size_t cap, size_t* len) {
@@ -1006,13 +1096,15 @@ int rosy_tex_submit_rgba8(const rosy_tex_desc* desc, const uint8_t* rgba, void* 
     if (rc) return rc;
     if ((rc = resolve(desc, r))) return rc;
     if (!rgba || !out) return fail(ROSY_TEX_ERR_ARG, "null buffer");
-    Job j;
-    j.desc = *desc;
-    j.rgba = rgba;
-    j.out = out;
-    j.cap = cap;
-    j.len = len;
-    return enqueue(std::move(j));
+    return guarded([&] {
+        Job j;
+        j.desc = *desc;
+        j.rgba = rgba;
+        j.out = out;
+        j.cap = cap;
+        j.len = len;
+        return enqueue(std::move(j));
+    });
 }
 
 int rosy_tex_wait_all(void) {
@@ -1094,9 +1186,20 @@ int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* 
 
 size_t rosy_tex_batch_scratch_size(int count) { return batch_desc_bytes(count); }
 
+}  // extern "C"
+static int encode_batch_device_impl(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
+                                    int do_mips, int do_blocks);
+extern "C" {
+
 int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
                                  int do_mips, int do_blocks) {
     if (!items || count <= 0) return fail(ROSY_TEX_ERR_ARG, "empty batch");
+    return guarded([&] { return encode_batch_device_impl(items, count, d_batch_scratch, stream, do_mips, do_blocks); });
+}
+}  // extern "C"
+
+static int encode_batch_device_impl(const rosy_tex_batch_item* items, int count, void* d_batch_scratch, void* stream,
+                                    int do_mips, int do_blocks) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     std::vector<Resolved> rs((size_t)count);
     std::vector<MipBatchItem> mi((size_t)count);
@@ -1120,6 +1223,7 @@ int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, int count, vo
     return encode_batch_on_stream(count, rs.data(), mi.data(), blk.data(), d_batch_scratch, s, do_mips != 0, do_blocks != 0);
 }
 
+extern "C" {
 uint64_t rosy_tex_kernel_launches(void) { return g_launches.load(); }
 
 }  // extern "C"

@@ -96,6 +96,77 @@ def test_jpeg_loader_matches_reference_stb_image_vectors(tex, tmp_path):
         assert (got == g["rgba_" + k]).all(), k
 
 
+def test_tga_loader_matches_reference_stb_image_vectors(tex, tmp_path):
+    """every TGA flavour the reference tree's stb_image.h reads (colour-mapped 1/9 with 15/16/24/32-bit
+    palettes and 8/16-bit indices, true colour 15/16/24/32, grey 8/16, raw + RLE, both origins) decodes to
+    stb's bytes; the FBX route (Fbx.cpp:421-474) feeds TGA exclusively"""
+    g = np.load(os.path.join(GOLD, "stb_image_tga.npz"))
+    keys = [k[4:] for k in g.files if k.startswith("tga_")]
+    assert len(keys) >= 24
+    for k in keys:
+        p = tmp_path / (k + ".tga")
+        p.write_bytes(g["tga_" + k].tobytes())
+        got = tex.load_image(str(p))
+        assert got.shape == g["rgba_" + k].shape, k
+        assert (got == g["rgba_" + k]).all(), k
+
+
+def test_hostile_headers_are_rejected_before_allocation(tex, tmp_path):
+    """a TGA / PNM header may not make the loader allocate (or index) past the file's payload"""
+    from rosy_b200 import RosyTexError
+
+    cases = {
+        "huge_raw.tga": bytes([0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0xFF, 0xFF, 0xFF, 0xFF, 32, 0]) + b"\0" * 64,
+        "huge_rle.tga": bytes([0, 0, 10, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0xFF, 0x7F, 0xFF, 0x7F, 32, 0]) + b"\xff" * 64,
+        "idlen_past_end.tga": bytes([200, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, 4, 0, 4, 0, 24, 0]) + b"\0" * 10,
+        "no_palette.tga": bytes([0, 1, 1, 0, 0, 0, 0, 24, 0, 0, 0, 0, 4, 0, 4, 0, 8, 0]) + b"\0" * 16,
+        "short_palette.tga": bytes([0, 1, 1, 0, 0, 0xFF, 0xFF, 24, 0, 0, 0, 0, 4, 0, 4, 0, 8, 0]) + b"\0" * 16,
+        "huge.ppm": b"P6\n4000000000 4000000000\n255\n" + b"\0" * 32,
+        "wrap.ppm": b"P6\n65536 65536\n255\n" + b"\0" * 32,
+    }
+    for name, data in cases.items():
+        p = tmp_path / name
+        p.write_bytes(data)
+        with pytest.raises(RosyTexError) as e:
+            tex.load_image(str(p))
+        assert e.value.status == 2, name
+
+
+def test_jpeg_malformed_huffman_tables_are_rejected(tex, tmp_path):
+    """an over-subscribed DHT (e.g. 255 codes of length 1) used to write far past the
+    9-bit look-ahead table; code lengths are now validated before any table entry is written"""
+    from rosy_b200 import RosyTexError
+
+    g = np.load(os.path.join(GOLD, "stb_image_jpeg.npz"))
+    good = g["jpg_64x48_420"].tobytes()
+    soi_rest = good[2:]
+
+    def dht(counts, nsym):
+        body = bytes([0x00]) + bytes(counts) + bytes(range(nsym % 256)) * (nsym // 256 + 1)
+        body = body[: 17 + nsym]
+        return b"\xff\xc4" + (len(body) + 2).to_bytes(2, "big") + body
+
+    bad = {
+        "len1_x255": dht([255] + [0] * 15, 255),
+        "len1_x3": dht([3] + [0] * 15, 3),
+        "len2_x5": dht([0, 5] + [0] * 14, 5),
+        "oversub_late": dht([1, 1, 1, 1, 1, 1, 1, 1, 3] + [0] * 7, 11),
+        "n256_len8": dht([0] * 7 + [255, 1] + [0] * 7, 256),
+    }
+    for name, seg in bad.items():
+        p = tmp_path / (name + ".jpg")
+        p.write_bytes(b"\xff\xd8" + seg + soi_rest)
+        if name == "n256_len8":  # 255 codes of length 8 + 1 of length 9 is a legal (complete-minus-one) table
+            try:
+                tex.load_image(str(p))
+            except RosyTexError as e:
+                assert e.status == 2
+            continue
+        with pytest.raises(RosyTexError) as e:
+            tex.load_image(str(p))
+        assert e.value.status == 2, name
+
+
 def test_jpeg_loader_rejects_bad_files(tex, tmp_path):
     from rosy_b200 import RosyTexError
 

@@ -160,3 +160,52 @@ def test_whole_stage_layout(oracle, synth):
         assert (dds[off : off + n] == oracle.encode_image(lvl, 0, 1)).all()
         off += n
     assert off == dds.size
+
+
+# ---- the BC7 search specification is frozen (VERDICT r1 task 1a) ---------------------------------------
+def blocks_to_image(px):
+    """(N, 64) RGBA8 4x4 blocks -> image 16 blocks wide whose row-major block order is the input order"""
+    n = px.shape[0]
+    assert n % 16 == 0
+    return px.reshape(n // 16, 16, 4, 4, 4).transpose(0, 2, 1, 3, 4).reshape(n // 16 * 4, 64, 4).copy()
+
+
+def test_bc7_encoder_reproduces_frozen_spec_v2(oracle):
+    """oracle/bc7.c still emits, bit for bit, the blocks committed as spec v2: the oracle cannot be
+    edited alongside the kernel without this failing (a new spec needs a new golden file)."""
+    g = np.load(os.path.join(GOLD, "bc7_spec_v2.npz"))
+    px = g["px"]
+    assert px.shape[0] >= 4096
+    img = blocks_to_image(px)
+    assert set(oracle.bc7_block_modes(g["high"].reshape(-1)).tolist()) == set(range(8))
+    for name, q in (("fast", oracle.Q_FAST), ("normal", oracle.Q_NORMAL), ("high", oracle.Q_HIGH)):
+        got = oracle.encode_image(img, oracle.FMT_BC7, q).reshape(-1, 16)
+        bad = np.nonzero((got != g[name]).any(axis=1))[0]
+        assert bad.size == 0, (name, bad[:8])
+
+
+# margins (dB) by which the product's `normal` tier may sit below the exhaustive ceiling, chain-weighted,
+# on the 128^2 test textures; measured values in profiles/r2_bc7_quality_gap.json (512^2) and BASELINE.md
+CEILING_MARGIN = {"albedo": 0.45, "albedo_cutout": 0.30, "normal": 1.50, "metal_rough": 2.30, "random": 0.20}
+
+
+@pytest.mark.parametrize("name,idx,kind", [("albedo", 0, 0), ("albedo_cutout", 7, 0), ("normal", 1, 1),
+                                           ("metal_rough", 2, 0), ("random", 3, 0)])
+def test_bc7_tiers_against_exhaustive_ceiling(oracle, synth, name, idx, kind):
+    """ORACLE_Q_EXHAUSTIVE (all partitions / rotations / p-bits, LS to convergence) bounds the tiers from
+    above; `high` must be within 0.2 dB of it and `normal` within the stated margin, per chain."""
+    img = synth.make("albedo" if name.startswith("albedo") else name, 128, 128, idx)
+    chain = oracle.mip_chain(img, kind)
+    sse = {q: 0 for q in (0, 1, 2, 3)}
+    n = 0
+    for lvl in chain:
+        h, w = lvl.shape[:2]
+        n += lvl.size
+        for q in sse:
+            dec = oracle.decode_image(oracle.encode_image(lvl, oracle.FMT_BC7, q), w, h)
+            d = lvl.astype(np.int64) - dec.astype(np.int64)
+            sse[q] += int((d * d).sum())
+    ps = {q: 99.0 if s == 0 else 10 * np.log10(255.0**2 * n / s) for q, s in sse.items()}
+    assert ps[0] <= ps[1] + 1e-9 <= ps[2] + 2e-9 <= ps[3] + 3e-9, ps
+    assert ps[2] >= ps[3] - 0.2, ps
+    assert ps[1] >= ps[3] - CEILING_MARGIN[name], ps
