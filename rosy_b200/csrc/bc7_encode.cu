@@ -24,7 +24,14 @@
 // in oracle/bc7.c (which the tests use as the checker; nothing here includes it).
 //
 // Tensor cores are not used: there is no dense contraction anywhere in the search.
+#ifdef BC7_HOST_EMU
+// tools/bc7_host_emu: the device functions of this file compiled for the host (one 4x4 block at a
+// time, NT = 1) so that every change to the search can be checked against tests/golden/bc7_spec_v2.npz
+// on a machine without a GPU.  Test tooling only; the product is the sm_100a build below.
+#include "bc7_host_emu.h"
+#else
 #include <cuda_runtime.h>
+#endif
 #include <stdint.h>
 
 #include <mutex>
@@ -51,14 +58,13 @@ namespace {
 #ifndef BC7_UP
 #define BC7_UP 4
 #endif
-#ifndef BC7_NT
-#define BC7_NT 512
+#ifndef BC7_MAGIC_I2F
+#define BC7_MAGIC_I2F 1
 #endif
 #ifndef BC7_JOB_SYNC
 #define BC7_JOB_SYNC 0
 #endif
 constexpr int EVAL_U2 = BC7_U2, EVAL_U3 = BC7_U3, EVAL_U4 = BC7_U4, PREP_U = BC7_UP;
-constexpr int NT = BC7_NT;   // threads (= blocks) per CTA
 constexpr int TOPK = 6;   // most partitions refined per mode (high tier)
 constexpr int MAXJOBS = 96;
 
@@ -85,6 +91,11 @@ enum { DEST_PART = 0, DEST_COLOUR = 1, DEST_SCALAR = 2 };
 //   pcmap = physical byte plane of logical channel c in nibble c
 __constant__ uint32_t c_VIEW_SEL[9] = {0x3210u, 0x4210u, 0x4213u, 0x4230u, 0x4310u,
                                        0x4443u, 0x4440u, 0x4441u, 0x4442u};
+//   inv   = __byte_perm selector that moves a palette entry in view order (logical channel k in byte k) to the
+//           texel's physical byte order (bytes the view does not use become zero): dot(view(p), e) == dot(p, inv(e)),
+//           so the index search reads the stored texels as they are and permutes the few palette entries instead
+__constant__ uint32_t c_VIEW_INV[9] = {0x3210u, 0x4210u, 0x0214u, 0x1240u, 0x2410u,
+                                       0x0444u, 0x4440u, 0x4404u, 0x4044u};
 __constant__ uint32_t c_VIEW_PC[9] = {0x3210u, 0x0210u, 0x0213u, 0x0230u, 0x0310u,
                                       0x0003u, 0x0000u, 0x0001u, 0x0002u};
 // w0: type[0:2] mode[2:5] ns[5:7] k[7:9] prow[9:15] view[15:19] nc[19:22] ib[22:25] bits[25:29] pbmode[29:31]
@@ -115,7 +126,10 @@ struct Params {
     uint64_t num_blocks;
 };
 
-// per-thread state columns
+// per-thread state columns.  NT = threads (= 4x4 blocks) per CTA: the kernel exists for several NT
+// (launch_bc7 picks the CTA size per launch so that the last wave of CTAs is as full as possible) and
+// for NT = 1 on the host (BC7_HOST_EMU).  Device functions take the instance as `SH`.
+template <int NT>
 struct Shared {
     uint32_t px[16][NT];   // texels, RGBA8
     uint32_t pl[16][NT];   // byte planes: [4*c + k] = channel c of texels 4k..4k+3
@@ -158,10 +172,11 @@ struct Prep {
     float lo[4], hi[4];
     int S1[4];
     int n;
+    int trace;  // sum over the subset's texels of |texel|^2 (view channels): the constant term of every fit error
 };
 
-template <int NC>
-__device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, uint32_t pcmap,
+template <int NC, class SH>
+__device__ __forceinline__ void prepare(const SH& S, int tid, uint32_t sel, uint32_t pcmap,
                                         uint32_t mask, Prep& P) {
     const int n = __popc(mask);
     int S1[NC], S2[NC][NC];
@@ -237,12 +252,28 @@ __device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, 
     float tmin = 3.0e38f, tmax = -3.0e38f, mv = 0.0f;
 #pragma unroll
     for (int c = 0; c < NC; c++) mv = __fmaf_rn(mean[c], v[c], mv);
+#if BC7_MAGIC_I2F
+    // byte -> float without the conversion unit: one PRMT drops view channel c of the stored texel into the
+    // mantissa of 2^23 (selector 4 reads the zero low byte of the constant: channels outside the view are 0),
+    // one FADD takes 2^23 off again; exact
+    uint32_t csel[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) csel[c] = 0x7440u | ((sel >> (4 * c)) & 7u);
+#endif
 #pragma unroll(PREP_U)
     for (int i = 0; i < 16; i++) {
+#if BC7_MAGIC_I2F
+        const uint32_t praw = S.px[i][tid];
+        float t = 0.0f;
+#pragma unroll
+        for (int c = 0; c < NC; c++)
+            t = __fmaf_rn(__uint_as_float(__byte_perm(praw, 0x4B000000u, csel[c])) - 8388608.0f, v[c], t);
+#else
         const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
         float t = 0.0f;
 #pragma unroll
         for (int c = 0; c < NC; c++) t = __fmaf_rn((float)((p >> (8 * c)) & 255u), v[c], t);
+#endif
         if ((mask >> i) & 1u) {
             tmin = t < tmin ? t : tmin;
             tmax = t > tmax ? t : tmax;
@@ -262,14 +293,21 @@ __device__ __forceinline__ void prepare(const Shared& S, int tid, uint32_t sel, 
         }
     }
     P.n = n;
+    int tr = 0;
+#pragma unroll
+    for (int a = 0; a < NC; a++) tr += S2[a][a];
+    P.trace = tr;
 }
 
 // ---- refine: quantise, exhaustive indices, least-squares rounds (spec v2 steps 4-6) ----------------
 
-// Integer SSD of the subset's texels against the palette of (e0, e1); exhaustive index search.
-template <int IB>
-__device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t sel, uint32_t mask,
-                                             uint32_t e0, uint32_t e1, uint64_t& idx_out) {
+// Exhaustive index search of the subset's texels against the palette of (e0, e1) (end points in view order).
+// Returns  sum over the subset of  min_j (|P_j|^2 - 2 p.P_j)  =  integer SSD - Prep::trace  (may be negative):
+// the texels' own |p|^2 does not depend on the end points and is added once per fit by the caller.
+// The palette entries are moved to the texels' byte order (`inv`), so the loop reads S.px as stored.
+template <int IB, class SH>
+__device__ __forceinline__ int evaluate(const SH& S, int tid, uint32_t inv, uint32_t mask,
+                                        uint32_t e0, uint32_t e1, uint64_t& idx_out) {
     constexpr int L = 1 << IB;
     uint32_t P[L];
     int K[L];
@@ -280,35 +318,35 @@ __device__ __forceinline__ uint32_t evaluate(const Shared& S, int tid, uint32_t 
         const uint32_t w = (uint32_t)weight_of<IB>(j);
         uint32_t rb = (((64u - w) * e0rb + w * e1rb + 0x00200020u) >> 6) & 0x00FF00FFu;
         uint32_t ga = (((64u - w) * e0ga + w * e1ga + 0x00200020u) >> 6) & 0x00FF00FFu;
-        P[j] = rb | (ga << 8);
-        K[j] = (dp4a_uu(P[j], P[j], 0) << 4) | j;
+        const uint32_t pv = rb | (ga << 8);
+        K[j] = (dp4a_uu(pv, pv, 0) << 4) | j;
+        P[j] = __byte_perm(pv, 0u, inv);
     }
     // Texels from 15 down to 0, eight per index word: the word is shifted up one nibble per texel
     // (one IMAD), the subset mask sits with the current texel's bit in the sign position.
-    uint32_t total = 0, word_hi = 0, word_lo = 0;
+    int total = 0;
+    uint32_t word_hi = 0, word_lo = 0;
     uint32_t m = mask << 16;
 #pragma unroll 1
     for (int h = 1; h >= 0; h--) {
         uint32_t acc = 0;
 #pragma unroll(IB == 2 ? EVAL_U2 : (IB == 3 ? EVAL_U3 : EVAL_U4))
         for (int i = 8 * h + 7; i >= 8 * h; i--) {
-            const uint32_t p = __byte_perm(S.px[i][tid], 0u, sel);
+            const uint32_t p = S.px[i][tid];
             int best = 0x7FFFFFFF;
 #pragma unroll
             for (int j = 0; j < L; j += 2)  // two entries per 3-input min (VIMNMX3)
                 best = __vimin3_s32(best, K[j] - (dp4a_uu(p, P[j], 0) << 5), K[j + 1] - (dp4a_uu(p, P[j + 1], 0) << 5));
-            best += dp4a_uu(p, p, 0) << 4;
-            const uint32_t in = (uint32_t)((int)m >> 31);  // all ones for a texel of the subset
+            const int in = (int)m >> 31;  // all ones for a texel of the subset
             m <<= 1;
-            const uint32_t b = (uint32_t)best & in;
+            const int b = best & in;      // 16 * (|P|^2 - 2 p.P) + index; the low nibble survives the sign
             total += b >> 4;
-            acc = acc * 16u + (b & 15u);
+            acc = acc * 16u + ((uint32_t)b & 15u);
         }
         word_hi = h ? acc : word_hi;
         word_lo = h ? word_lo : acc;
     }
-    const uint64_t idx = ((uint64_t)word_hi << 32) | word_lo;
-    idx_out = idx;
+    idx_out = ((uint64_t)word_hi << 32) | word_lo;
     return total;
 }
 
@@ -327,23 +365,29 @@ __device__ __forceinline__ uint32_t weight_bytes(uint32_t nib16) {
     return (wl & ~h) | (wh & h);
 }
 
+// floor of a float in [0, 2^23) without the conversion unit: a round-down add of 2^23 leaves the integer in
+// the low mantissa bits (FADD.RM + LOP instead of F2I.FLOOR on the quarter-rate pipe)
+constexpr float FLOOR_MAGIC = 8388608.0f;
+__device__ __forceinline__ int floor_small(float t) {
+    return (int)(__float_as_uint(__fadd_rd(t, FLOOR_MAGIC)) & 0x1FFu);  // callers stay below 512
+}
 // end-point channel x in [0,255] -> field value; `scale` = (2^(bits+1) - 1) / 255 with a p-bit
-// (LSB forced to p), (2^bits - 1) / 255 without
+// (LSB forced to p), (2^bits - 1) / 255 without.  The rounded argument is never negative
+// ((y - 1) / 2 + 1/2 >= 0 for y >= 0), so only the upper clamp of the specification can act.
 __device__ __forceinline__ int quant_pbit(float x, float scale, int maxq, int p) {
     const float y = x * scale;
-    const int q = (int)floorf(__fmaf_rn(y - (float)p, 0.5f, 0.5f));  // halving is exact: same value as mul, add
-    return min(max(q, 0), maxq);
+    return min(floor_small(__fmaf_rn(y - (float)p, 0.5f, 0.5f)), maxq);  // halving is exact: same value as mul, add
 }
 __device__ __forceinline__ int quant_plain(float x, float scale, int maxq) {
-    const int q = (int)floorf(x * scale + 0.5f);
-    return min(max(q, 0), maxq);
+    return min(floor_small(x * scale + 0.5f), maxq);
 }
 
 // One fit after `prepare`: quantise (p-bit by nearest end point, or every combination when
 // pb_search), exhaustive indices, then `ls_rounds` least-squares refinements (spec v2 steps 4-6).
 // Only `evaluate` and the weight lookup depend on the index width, so they are the only code that
 // exists per width.
-__device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, uint32_t pcmap,
+template <class SH>
+__device__ __forceinline__ void refine(const SH& S, int tid, uint32_t inv, uint32_t pcmap,
                                        uint32_t mask, int ib, int nc, int bits, int pbmode,
                                        int ls_rounds, int pb_search, Prep& P, Fit& out) {
     out.err = 0xFFFFFFFFu;
@@ -401,13 +445,17 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
                     for (int c = 0; c < 4; c++) {
                         if (c < nc) {
                             const float x = e ? P.hi[c] : P.lo[c];
-                            int q = quant_pbit(x, scale, maxq, 0);
+                            // both quantisations from one product: p = 0 is floor(y/2 + 1/2) (at most maxq + 1),
+                            // p = 1 is floor(fma(y - 1, 1/2, 1/2)) == floor(y/2) <= maxq for every y >= 0 (y - 1 is
+                            // exact for y >= 1 and the result is 0 either way below that)
+                            const float y = x * scale;
+                            int q = min(floor_small(__fmaf_rn(y, 0.5f, 0.5f)), maxq);
                             int ex = expand_bits(q << 1, bits + 1);
                             float d = (float)ex - x;
                             const float d0 = d * d;
                             qq[e][0] |= (uint32_t)q << (8 * c);
                             ee[e][0] |= (uint32_t)ex << (8 * c);
-                            q = quant_pbit(x, scale, maxq, 1);
+                            q = floor_small(y * 0.5f);
                             ex = expand_bits((q << 1) | 1, bits + 1);
                             d = (float)ex - x;
                             const float d1 = d * d;
@@ -464,13 +512,14 @@ __device__ __forceinline__ void refine(const Shared& S, int tid, uint32_t sel, u
             e0 &= chmask;
             e1 &= chmask;
             uint64_t idx;
-            uint32_t err;
+            int rel;
             if (ib == 2)
-                err = evaluate<2>(S, tid, sel, mask, e0, e1, idx);
+                rel = evaluate<2>(S, tid, inv, mask, e0, e1, idx);
             else if (ib == 3)
-                err = evaluate<3>(S, tid, sel, mask, e0, e1, idx);
+                rel = evaluate<3>(S, tid, inv, mask, e0, e1, idx);
             else
-                err = evaluate<4>(S, tid, sel, mask, e0, e1, idx);
+                rel = evaluate<4>(S, tid, inv, mask, e0, e1, idx);
+            const uint32_t err = (uint32_t)(rel + P.trace);
             if (err < out.err) {
                 out.err = err;
                 out.q0 = q0;
@@ -583,8 +632,8 @@ __device__ __forceinline__ void masked_moments(const uint32_t pl[4][4], const ui
 
 // Rank the partitions of a 2- or 3-subset table for two index widths at once; the best TOPK of
 // each list go to S.parts rows rowA.. and rowB.. (rowB < 0: second list not wanted).
-template <int NC, int NS>
-__device__ __forceinline__ void estimate_partitions(Shared& S, int tid, int nparts, int ibA, int ibB,
+template <int NC, int NS, class SH>
+__device__ __forceinline__ void estimate_partitions(SH& S, int tid, int nparts, int ibA, int ibB,
                                                     int rowA, int rowB) {
     uint32_t pl[4][4];
 #pragma unroll
@@ -692,7 +741,8 @@ __device__ __forceinline__ void swap_endpoint_bytes(uint32_t& a, uint32_t& b, ui
 }
 
 // the thread's best solution (S.best column) -> 128-bit block
-__device__ __forceinline__ uint4 pack_solution(const Shared& S, int tid) {
+template <class SH>
+__device__ __forceinline__ uint4 pack_solution(const SH& S, int tid) {
     uint32_t q[3][2];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -780,60 +830,11 @@ __device__ __forceinline__ uint4 pack_solution(const Shared& S, int tid) {
 
 // ---- kernel ----------------------------------------------------------------------------------
 
-#ifndef BC7_MIN_CTAS
-#define BC7_MIN_CTAS (512 / BC7_NT)
-#endif
-// One texture (P1, plist == nullptr) or a batch of textures of one quality tier: plist[t] describes
-// texture t, whose blocks are threads base[t] .. base[t+1]-1 of the launch.  A CTA may straddle two
-// textures: every thread is independent.
-__global__ void __launch_bounds__(NT, BC7_MIN_CTAS)
-bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ plist,
-                  const uint64_t* __restrict__ base_of, int ntex) {
-    extern __shared__ __align__(16) uint8_t bc7_smem[];
-    Shared& S = *reinterpret_cast<Shared*>(bc7_smem);
-    const int tid = threadIdx.x;
-    uint64_t b = (uint64_t)blockIdx.x * NT + tid;
-    const Params* Pp = &P1;
-    if (plist) {
-        int lo = 0, hi = ntex;  // base_of[lo] <= b < base_of[hi]  (threads past the end use the last texture)
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (b >= base_of[mid]) lo = mid; else hi = mid;
-        }
-        Pp = plist + lo;
-        b -= base_of[lo];
-    }
-    const Params& P = *Pp;
-    const bool live = b < P.num_blocks;
-    uint4* const outp = live ? reinterpret_cast<uint4*>(P.out) + b : nullptr;  // the only thing kept of P and b
-    // which level does this block belong to?
-    const uint64_t gb = P.first_block + (live ? b : 0);
-    int level = P.first_level;
-    for (int l = P.first_level + 1; l < P.first_level + P.num_levels; l++)
-        if (gb >= P.chain.lv[l].blk_offset) level = l;
-    const Level lv = P.chain.lv[level];
-    const uint32_t lb = (uint32_t)(gb - lv.blk_offset);
-    const uint32_t bx = lb % lv.bw, by = lb / lv.bw;
-    const uint8_t* base = (level == 0 && P.level0) ? P.level0 : P.chainbuf + 4ull * lv.px_offset;
-    // load the 4x4 texels (partial blocks repeat the edge texels)
-    if (4 * bx + 3 < lv.w && 4 * by + 3 < lv.h && (lv.w & 3u) == 0 && ((uintptr_t)base & 15u) == 0) {
-#pragma unroll
-        for (int y = 0; y < 4; y++) {
-            const uint4 r = __ldg(reinterpret_cast<const uint4*>(
-                base + 4ull * ((uint64_t)(4 * by + y) * lv.w + 4 * bx)));
-            S.px[4 * y + 0][tid] = r.x;
-            S.px[4 * y + 1][tid] = r.y;
-            S.px[4 * y + 2][tid] = r.z;
-            S.px[4 * y + 3][tid] = r.w;
-        }
-    } else {
-        for (int y = 0; y < 4; y++)
-            for (int x = 0; x < 4; x++) {
-                const uint32_t sx = min(4 * bx + x, lv.w - 1), sy = min(4 * by + y, lv.h - 1);
-                S.px[4 * y + x][tid] =
-                    __ldg(reinterpret_cast<const uint32_t*>(base) + (uint64_t)sy * lv.w + sx);
-            }
-    }
+// The search for the 4x4 block whose texels sit in column `tid` of S.px (spec v2) -> the
+// 128-bit block.  tier / ls / pbs are uniform over the launch, so the job decode stays uniform.
+template <class SH>
+__device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool live, const int tier, const int ls,
+                                               const int pbs) {
     // every thread only ever touches its own column of S: no barrier needed anywhere
     const uint32_t p0 = S.px[0][tid];
     bool solid = true, has_alpha = false;
@@ -870,10 +871,6 @@ bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ 
         S.best[11][tid] = 5u;
     }
     const bool search = live && !solid;
-    // the job list is the same for every thread of the launch: tier / ls / pbs come from the kernel's
-    // own parameter (uniform), never from a per-texture descriptor, so the job decode stays uniform
-    const int tier = P1.tier;
-    const int ls = P1.ls_rounds, pbs = P1.pb_search;
     // candidate under construction
     uint32_t cq[3][2] = {{0, 0}, {0, 0}, {0, 0}}, cpb = 0, cerr = 0;
     uint64_t cidx = 0, cidx2 = 0;
@@ -909,6 +906,7 @@ bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ 
                 S.p3[4 + c][tid] = __float_as_uint(pr.hi[c]);
                 S.p3[8 + c][tid] = (uint32_t)pr.S1[c];
             }
+            S.p3[11][tid] = (uint32_t)pr.trace;  // S1[3] of the RGB view is zero by construction: its slot carries the trace
             continue;
         }
         // ---- a fit ----
@@ -942,13 +940,16 @@ bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ 
                 pr.S1[c] = (int)S.p3[8 + c][tid];
             }
             pr.n = 16;
+            pr.trace = pr.S1[3];
+            pr.S1[3] = 0;
             if (prep == PREP_MODE6) {  // opaque block: the RGBA fit is the RGB fit with alpha = 255
                 pr.lo[3] = pr.hi[3] = 255.0f;
                 pr.S1[3] = 16 * 255;
+                pr.trace += 16 * 255 * 255;
             }
         }
         Fit f;
-        refine(S, tid, sel, pcmap, mask, ib, nc, bits, pbmode, ls, pbs, pr, f);
+        refine(S, tid, c_VIEW_INV[view], pcmap, mask, ib, nc, bits, pbmode, ls, pbs, pr, f);
         // ---- accumulate into the candidate ----
         if (first) {
 #pragma unroll
@@ -1003,8 +1004,67 @@ bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ 
             S.best[11][tid] = (uint32_t)mode | ((uint32_t)partition << 3) | ((uint32_t)rot << 9) | ((uint32_t)idxsel << 11);
         }
     }
-    if (outp) *outp = pack_solution(S, tid);
+    return pack_solution(S, tid);
 }
+
+#ifndef BC7_HOST_EMU
+// One texture (P1, plist == nullptr) or a batch of textures of one quality tier: plist[t] describes
+// texture t, whose blocks are threads base[t] .. base[t+1]-1 of the launch.  A CTA may straddle two
+// textures: every thread is independent.
+template <int NT>
+__global__ void __launch_bounds__(NT, 1)
+bc7_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__ plist,
+                  const uint64_t* __restrict__ base_of, int ntex) {
+    extern __shared__ __align__(16) uint8_t bc7_smem[];
+    Shared<NT>& S = *reinterpret_cast<Shared<NT>*>(bc7_smem);
+    const int tid = threadIdx.x;
+    uint64_t b = (uint64_t)blockIdx.x * NT + tid;
+    const Params* Pp = &P1;
+    if (plist) {
+        int lo = 0, hi = ntex;  // base_of[lo] <= b < base_of[hi]  (threads past the end use the last texture)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (b >= base_of[mid]) lo = mid; else hi = mid;
+        }
+        Pp = plist + lo;
+        b -= base_of[lo];
+    }
+    const Params& P = *Pp;
+    const bool live = b < P.num_blocks;
+    uint4* const outp = live ? reinterpret_cast<uint4*>(P.out) + b : nullptr;  // the only thing kept of P and b
+    // which level does this block belong to?
+    const uint64_t gb = P.first_block + (live ? b : 0);
+    int level = P.first_level;
+    for (int l = P.first_level + 1; l < P.first_level + P.num_levels; l++)
+        if (gb >= P.chain.lv[l].blk_offset) level = l;
+    const Level lv = P.chain.lv[level];
+    const uint32_t lb = (uint32_t)(gb - lv.blk_offset);
+    const uint32_t bx = lb % lv.bw, by = lb / lv.bw;
+    const uint8_t* base = (level == 0 && P.level0) ? P.level0 : P.chainbuf + 4ull * lv.px_offset;
+    // load the 4x4 texels (partial blocks repeat the edge texels)
+    if (4 * bx + 3 < lv.w && 4 * by + 3 < lv.h && (lv.w & 3u) == 0 && ((uintptr_t)base & 15u) == 0) {
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            const uint4 r = __ldg(reinterpret_cast<const uint4*>(
+                base + 4ull * ((uint64_t)(4 * by + y) * lv.w + 4 * bx)));
+            S.px[4 * y + 0][tid] = r.x;
+            S.px[4 * y + 1][tid] = r.y;
+            S.px[4 * y + 2][tid] = r.z;
+            S.px[4 * y + 3][tid] = r.w;
+        }
+    } else {
+        for (int y = 0; y < 4; y++)
+            for (int x = 0; x < 4; x++) {
+                const uint32_t sx = min(4 * bx + x, lv.w - 1), sy = min(4 * by + y, lv.h - 1);
+                S.px[4 * y + x][tid] =
+                    __ldg(reinterpret_cast<const uint32_t*>(base) + (uint64_t)sy * lv.w + sx);
+            }
+    }
+    // every thread only ever touches its own column of S: no barrier needed anywhere
+    const uint4 blk = encode_texels(S, tid, live, P1.tier, P1.ls_rounds, P1.pb_search);
+    if (outp) *outp = blk;
+}
+#endif  // !BC7_HOST_EMU
 
 }  // namespace
 
@@ -1131,14 +1191,72 @@ int bc7_upload_tables() {
     return e == cudaSuccess ? 0 : -1;
 }
 
-// function attributes are per device: set once on each device that launches
-static void prepare_launch() {
-    static std::once_flag once[64];
+#ifndef BC7_HOST_EMU
+// ---- CTA size per launch ---------------------------------------------------------------------
+// One CTA per SM (registers), so a launch runs in waves of SMs x NT blocks and a mostly empty last wave
+// costs as much as a full one: one 1024^2 chain is 87 383 blocks = 1.15 waves of 148 x 512 and ran at 52 %
+// of the batched rate.  The kernel therefore exists for three CTA sizes and every launch takes the one
+// with the smallest modelled time  ceil(blocks / (SMs * NT)) * wave_time(NT):
+//   NT 640 (96 registers)   one 1024^2 chain fits ONE wave of 148 x 640
+//   NT 512 (128 registers)  the steady-state size (long launches: whichever is ahead by the model, ties -> 512)
+//   NT 256                  launches of less than one 148 x 256 wave: half the warps per scheduler, so each
+//                           block finishes sooner (latency, not throughput, is what a short launch waits for)
+// wave_time is relative to NT 512; ROSY_TEX_BC7_NT=<256|512|640> forces a size (A/B runs).
+template <int NT>
+static cudaError_t launch_nt(uint64_t nblocks, const Params& p1, const Params* d_ps, const uint64_t* d_base, int ntex,
+                             cudaStream_t s) {
+    static std::once_flag once[64];  // function attributes are per device: set once on each device that launches
     int dev = 0;
     cudaGetDevice(&dev);
     std::call_once(once[dev & 63], [] {
-        cudaFuncSetAttribute(bc7_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared));
+        cudaFuncSetAttribute(bc7_encode_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared<NT>));
     });
+    const uint64_t grid = (nblocks + NT - 1) / NT;
+    bc7_encode_kernel<NT><<<(unsigned)grid, NT, sizeof(Shared<NT>), s>>>(p1, d_ps, d_base, ntex);
+    return cudaGetLastError();
+}
+
+static int sm_count() {
+    static int sms[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& n = sms[dev & 63];
+    if (n == 0 && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 148;
+    return n > 0 ? n : 148;
+}
+
+int bc7_pick_cta_size(uint64_t nblocks, int sms) {
+    static const int forced = [] {
+        const char* e = getenv("ROSY_TEX_BC7_NT");
+        const int v = e ? atoi(e) : 0;
+        return (v == 256 || v == 512 || v == 640) ? v : 0;
+    }();
+    if (forced) return forced;
+    struct V { int nt; double wave; };
+    // wave_time(640) = 640/512 / 1.006 (measured r1: 640 threads at 96 registers is 0.6 % ahead per block)
+    static const V v[3] = {{512, 1.0}, {640, 1.2425}, {256, 0.56}};
+    int best = 512;
+    double best_t = 0.0;
+    for (int i = 0; i < 3; i++) {
+        const uint64_t per_wave = (uint64_t)sms * (uint64_t)v[i].nt;
+        const uint64_t waves = (nblocks + per_wave - 1) / per_wave;
+        if (v[i].nt == 256 && waves > 1) continue;  // only for launches below one small wave
+        const double t = (double)waves * v[i].wave;
+        if (i == 0 || t < best_t * 0.995) {  // ties (within 0.5 %) keep the earlier entry
+            best = v[i].nt;
+            best_t = t;
+        }
+    }
+    return best;
+}
+
+static cudaError_t launch_any(uint64_t nblocks, const Params& p1, const Params* d_ps, const uint64_t* d_base, int ntex,
+                              cudaStream_t s) {
+    switch (bc7_pick_cta_size(nblocks, sm_count())) {
+        case 640: return launch_nt<640>(nblocks, p1, d_ps, d_base, ntex, s);
+        case 256: return launch_nt<256>(nblocks, p1, d_ps, d_base, ntex, s);
+        default: return launch_nt<512>(nblocks, p1, d_ps, d_base, ntex, s);
+    }
 }
 
 static void fill_params(Params& P, const Chain& c, int first_level, int num_levels, int quality,
@@ -1152,7 +1270,6 @@ size_t bc7_batch_desc_bytes(int n) {
 // BC7 blocks of n textures (all levels each): one launch per quality tier present.  d_desc:
 // bc7_batch_desc_bytes(n) bytes of device memory that must stay untouched until the launches ran.
 int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_t s) {
-    prepare_launch();
     int launches = 0;
     uint8_t* dd = reinterpret_cast<uint8_t*>(d_desc);
     size_t used = 0;
@@ -1180,9 +1297,7 @@ int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_
         if (cudaMemcpyAsync(d_ps, ps.data(), ps.size() * sizeof(Params), cudaMemcpyHostToDevice, s) != cudaSuccess ||
             cudaMemcpyAsync(d_base, base.data(), base.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, s) != cudaSuccess)
             return -1;
-        const uint64_t grid = (total + NT - 1) / NT;
-        bc7_encode_kernel<<<(unsigned)grid, NT, sizeof(Shared), s>>>(ps[0], d_ps, d_base, (int)ps.size());
-        if (cudaGetLastError() != cudaSuccess) return -1;
+        if (launch_any(total, ps[0], d_ps, d_base, (int)ps.size(), s) != cudaSuccess) return -1;
         launches++;
     }
     return launches;
@@ -1208,10 +1323,34 @@ int launch_bc7(const Chain& c, int first_level, int num_levels, int quality, con
                const uint8_t* d_chain, uint8_t* d_blocks, cudaStream_t s) {
     Params P;
     fill_params(P, c, first_level, num_levels, quality, d_level0, d_chain, d_blocks);
-    const uint64_t grid = (P.num_blocks + NT - 1) / NT;
-    prepare_launch();
-    bc7_encode_kernel<<<(unsigned)grid, NT, sizeof(Shared), s>>>(P, nullptr, nullptr, 1);
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    return launch_any(P.num_blocks, P, nullptr, nullptr, 1, s) == cudaSuccess ? 1 : -1;
 }
 
+#else   // BC7_HOST_EMU: one block at a time through the same device functions
+}  // namespace rosy_tex
+extern "C" int bc7_emu_encode_image(const uint8_t* rgba, int w, int h, int quality, uint8_t* blocks) {
+    using namespace rosy_tex;
+    static bool ready = false;
+    if (!ready) {
+        if (bc7_upload_tables() != 0) return -1;
+        ready = true;
+    }
+    const Bc7Tier t = bc7_tier(quality);
+    const int tier = quality < 0 ? 0 : (quality > 2 ? 2 : quality);
+    const int bw = (w + 3) / 4, bh = (h + 3) / 4;
+    static Shared<1> S;
+    for (int by = 0; by < bh; by++)
+        for (int bx = 0; bx < bw; bx++) {
+            for (int y = 0; y < 4; y++)
+                for (int x = 0; x < 4; x++) {
+                    const int sx = 4 * bx + x < w ? 4 * bx + x : w - 1, sy = 4 * by + y < h ? 4 * by + y : h - 1;
+                    memcpy(&S.px[4 * y + x][0], rgba + 4 * ((size_t)sy * w + sx), 4);
+                }
+            const uint4 blk = encode_texels(S, 0, true, tier, t.ls_rounds, t.pb_search);
+            memcpy(blocks + 16 * ((size_t)by * bw + bx), &blk, 16);
+        }
+    return 0;
+}
+namespace rosy_tex {
+#endif  // BC7_HOST_EMU
 }  // namespace rosy_tex

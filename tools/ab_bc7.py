@@ -26,7 +26,11 @@ def run(kind_name, kind, q, n=2048, reps=10):
     # parity spot check on a crop (bit exact vs the oracle)
     crop = np.ascontiguousarray(img[:64, :64])
     ok = (T.compress_level(crop, 0, q) == O.encode_image(crop, 0, q)).all()
-    print(f"{os.path.basename(T.LIB_PATH):12s} {kind_name:8s} q{q} {n}x{n} blocks {ms:8.3f} ms {n*n/ms/1e3:9.1f} Mpix/s exact={ok}", flush=True)
+    print(f"NT={os.environ.get('ROSY_TEX_BC7_NT', 'auto'):5s} {os.path.basename(T.LIB_PATH):12s} {kind_name:8s} q{q} {n}x{n} blocks {ms:8.3f} ms {n*n/ms/1e3:9.1f} Mpix/s exact={ok}", flush=True)
 
 if __name__ == "__main__":
-    run("albedo", 0, 1); run("albedo", 0, 0); run("albedo", 0, 2, reps=3); run("normal", 1, 1)
+    if len(sys.argv) > 1 and sys.argv[1] == "sizes":  # single-texture launches: the CTA size choice (ROSY_TEX_BC7_NT forces one)
+        for n in (256, 512, 1024, 2048, 4096):
+            run("albedo", 0, 1, n=n, reps=20 if n <= 1024 else 5)
+    else:
+        run("albedo", 0, 1); run("albedo", 0, 0); run("albedo", 0, 2, reps=3); run("normal", 1, 1)
