@@ -1197,11 +1197,12 @@ int bc7_upload_tables() {
 // costs as much as a full one: one 1024^2 chain is 87 383 blocks = 1.15 waves of 148 x 512 and ran at 52 %
 // of the batched rate.  The kernel therefore exists for three CTA sizes and every launch takes the one
 // with the smallest modelled time  ceil(blocks / (SMs * NT)) * wave_time(NT):
-//   NT 640 (96 registers)   one 1024^2 chain fits ONE wave of 148 x 640
-//   NT 512 (128 registers)  the steady-state size (long launches: whichever is ahead by the model, ties -> 512)
-//   NT 256                  launches of less than one 148 x 256 wave: half the warps per scheduler, so each
-//                           block finishes sooner (latency, not throughput, is what a short launch waits for)
-// wave_time is relative to NT 512; ROSY_TEX_BC7_NT=<256|512|640> forces a size (A/B runs).
+//   NT 512 (128 registers)  the steady-state size: best time per block
+//   NT 640 (96 registers)   one 1024^2 chain fits ONE wave of 148 x 640 (0.424 -> 0.276 ms, measured)
+//   NT 256                  launches below one 148 x 256 wave: fewer warps per scheduler, each block finishes
+//                           sooner (512^2 chain 0.220 -> 0.151 ms): a short launch waits for latency, not throughput
+// wave_time relative to NT 512, measured on B200 (profiles/r2b_ab.log: 4096^2 chain 3.982 ms in 19 waves of 512,
+// 4.019 ms in 15 waves of 640; 512^2 chain in one wave of 256).  ROSY_TEX_BC7_NT=<256|512|640> forces a size.
 template <int NT>
 static cudaError_t launch_nt(uint64_t nblocks, const Params& p1, const Params* d_ps, const uint64_t* d_base, int ntex,
                              cudaStream_t s) {
@@ -1233,8 +1234,7 @@ int bc7_pick_cta_size(uint64_t nblocks, int sms) {
     }();
     if (forced) return forced;
     struct V { int nt; double wave; };
-    // wave_time(640) = 640/512 / 1.006 (measured r1: 640 threads at 96 registers is 0.6 % ahead per block)
-    static const V v[3] = {{512, 1.0}, {640, 1.2425}, {256, 0.56}};
+    static const V v[3] = {{512, 1.0}, {640, 1.275}, {256, 0.72}};
     int best = 512;
     double best_t = 0.0;
     for (int i = 0; i < 3; i++) {
