@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=2, help="textures in the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
+    ap.add_argument("--files", type=int, default=16, help="image files in the e2e_files leg (0: skip)")
     ap.add_argument("--per-texture", action="store_true",
                     help="device leg: one mip launch per texture (rosy_tex_mips_device) instead of the batched call")
     return ap.parse_args()
@@ -190,6 +191,10 @@ def run_reference_arm(args, rank):
     sec = float(np.mean(times))
     mpix = len(sample) * args.size * args.size / 1e6
     value = mpix / sec
+    sec1 = cpu_oracle_run(sample, args.kind, fmt, q, threads=1)
+    cfg = workload_config(args, args.textures)
+    cfg["sample"] = (f"each timed step of this arm is 1 of the workload's {args.textures} textures per GPU "
+                     "(bounded CPU sample; the metric is per pixel, so the value is comparable)")
     line = {
         "impl": "reference",
         "metric": METRIC,
@@ -204,13 +209,15 @@ def run_reference_arm(args, rank):
         "vs_baseline": None,
         "dtype": "u8+fp32",
         "data": "synthetic",
-        "config": workload_config(args, args.textures),
+        "config": cfg,
         "cpu_baseline": {
             "value": value,
             "unit": UNIT,
             "cores": cores,
+            "value_1t": mpix / sec1,
             "kind": "port",
-            "sample": f"1 x {args.size}x{args.size} {args.kind}, full mips + {args.format.upper()} {args.quality}, per step",
+            "sample": f"1 x {args.size}x{args.size} {args.kind}, full mips + {args.format.upper()} {args.quality}, per step; "
+            "mip rows and blocks both shared by all host threads; value_1t = the same texture on 1 thread",
         },
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -259,10 +266,9 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # NCCL is plumbing here (barrier + MAX of the times): keep its banner off stdout, which carries the JSON line
-        if not os.environ.get("ROSY_KEEP_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=dev)
+        # The path has no exchange step: the only multi-rank traffic of this script is the barrier and
+        # the MAX of the times, which go over gloo on the host.  NCCL is not initialised anywhere (north_star).
+        dist.init_process_group("gloo")
 
     fmt = {"bc7": T.FORMAT_BC7, "bc5": T.FORMAT_BC5, "bc4": T.FORMAT_BC4}[args.format]
     q = {"fast": 0, "normal": 1, "high": 2}[args.quality]
@@ -287,7 +293,7 @@ def main():
     def max_over_ranks(x):
         if world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        t = torch.tensor([x], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
@@ -413,6 +419,12 @@ def main():
         for p in host_in + host_out:
             L.rosy_tex_free_host(p)
 
+    # ---------------- e2e_files leg: image files -> .dds files through rosy_tex_submit -----------
+    # (the reference interface itself: generate_*_texture(path), Packager.cpp:216,263; decode + write included)
+    e2e_files = None
+    if rank == 0 and world == 1 and args.files > 0 and not args.no_e2e:
+        e2e_files = files_leg(T, textures[: min(args.files, n)], kind, size)
+
     # ---------------- roofline of the dominant kernel ----------------------------------------
     peaks = {}
     try:
@@ -477,14 +489,17 @@ def main():
         import oracle as O
 
         sample = textures[: max(1, args.cpu_sample)]
-        sec = cpu_oracle_run(sample, args.kind, fmt, q)
+        sec = cpu_oracle_run(sample, args.kind, fmt, q)  # every core: mip rows and blocks both threaded
+        sec1 = cpu_oracle_run(sample[:1], args.kind, fmt, q, threads=1)
         cpu = {
             "value": len(sample) * npx / 1e6 / sec,
             "unit": UNIT,
             "cores": O.max_threads(),
+            "value_1t": npx / 1e6 / sec1,
             "kind": "port",
             "sample": f"{len(sample)} of the step's {n} textures ({size}x{size} {args.kind}, full mips + "
-            f"{args.format.upper()} {args.quality}), {sec:.1f} s of CPU work",
+            f"{args.format.upper()} {args.quality}), {sec:.1f} s on all cores; value_1t: 1 texture on 1 thread, {sec1:.1f} s; "
+            "oracle/ built -O3 -march=x86-64-v3 (the .so travels between hosts, so not -march=native)",
         }
 
     if rank == 0:
@@ -503,6 +518,7 @@ def main():
             "data": "synthetic",
             "config": workload_config(args, n),
             "e2e": e2e,
+            "e2e_files": e2e_files,
             "gpu_launches": int(launches),
             "roofline": roofline,
             "roofline_mip": roofline_mip,
@@ -514,6 +530,42 @@ def main():
     if world > 1:
         dist.destroy_process_group()
     T.shutdown()
+
+
+def files_leg(T, images, kind, size):
+    """PNG / JPEG files on disk -> .dds files next to them (decode threads -> pinned staging -> device slots ->
+    writer threads).  Decode-bound on the host; reported beside `e2e`, whose inputs are already decoded."""
+    import shutil
+    import tempfile
+
+    from PIL import Image
+
+    d = tempfile.mkdtemp(prefix="rosy_bench_files_")
+    try:
+        paths = []
+        for i, img in enumerate(images):
+            if i % 2:
+                p = os.path.join(d, f"t{i}.jpg")
+                Image.fromarray(img[..., :3]).save(p, quality=90)
+            else:
+                p = os.path.join(d, f"t{i}.png")
+                Image.fromarray(img).save(p, compress_level=1)
+            paths.append(p)
+        in_bytes = sum(os.path.getsize(p) for p in paths)
+        T.submit_file(paths[0], kind)  # warm-up: I/O threads, pinned pool
+        T.wait_all()
+        t0 = time.perf_counter()
+        for p in paths:
+            T.submit_file(p, kind)
+        T.wait_all()
+        sec = time.perf_counter() - t0
+        out_bytes = sum(os.path.getsize(os.path.splitext(p)[0] + ".dds") for p in paths)
+        return {"value": len(paths) * size * size / 1e6 / sec, "unit": UNIT, "files": len(paths),
+                "formats": "PNG (even) / JPEG q90 (odd)", "input_file_bytes": in_bytes, "output_file_bytes": out_bytes,
+                "seconds": sec, "io_threads": int(os.environ.get("ROSY_TEX_IO_THREADS", os.cpu_count() or 1)),
+                "api": "rosy_tex_submit(path) + rosy_tex_wait_all: file decode and .dds write inside the timed region"}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
 
 
 def load_profile_counts(args):

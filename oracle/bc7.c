@@ -911,10 +911,10 @@ size_t oracle_generate_texture(const uint8_t* rgba, int w, int h, int kind, int 
                                int normalize_mode, uint8_t* dds_out, int threads) {
     const int levels = oracle_count_mipmaps(w, h);
     uint8_t* chain = (uint8_t*)malloc(4 * oracle_chain_pixels(w, h));
-    if (kind == ORACLE_KIND_NORMAL)
-        oracle_mip_chain_normal(rgba, w, h, normalize_mode, chain);
+    if (kind == ORACLE_KIND_NORMAL) /* the chain's rows and the blocks are both shared by `threads` host threads */
+        oracle_mip_chain_normal_mt(rgba, w, h, normalize_mode, chain, threads);
     else
-        oracle_mip_chain_srgb(rgba, w, h, chain);
+        oracle_mip_chain_srgb_mt(rgba, w, h, chain, threads);
     oracle_dds_header(w, h, levels, fmt, dds_out); /* :237 / :286 */
     uint8_t* dst = dds_out + ORACLE_DDS_HEADER_BYTES;
     const uint8_t* src = chain;

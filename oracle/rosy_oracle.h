@@ -52,6 +52,10 @@ size_t oracle_chain_blocks(int w, int h);
 void oracle_mip_chain_srgb(const uint8_t* rgba, int w, int h, uint8_t* out);
 /* Normal chain, Packager.cpp:292-306. */
 void oracle_mip_chain_normal(const uint8_t* rgba, int w, int h, int normalize_mode, uint8_t* out);
+/* The same chains with the rows of every pass shared by `threads` host threads (<= 0: all cores); results
+ * are identical for every thread count (the passes are element-wise or row-local). */
+void oracle_mip_chain_srgb_mt(const uint8_t* rgba, int w, int h, uint8_t* out, int threads);
+void oracle_mip_chain_normal_mt(const uint8_t* rgba, int w, int h, int normalize_mode, uint8_t* out, int threads);
 
 /* --- BC7 (public BPTC spec) --- */
 void oracle_bc7_decode_block(const uint8_t blk[16], uint8_t rgba[64]);

@@ -4,9 +4,14 @@
 //   rosy_packager_tex [--serial] [--dry-run] [--all-textures] <file.gltf>          the image part of `Packager.exe <file.gltf>`
 //       (Main.cpp:126-174 -> Gltf.cpp:97-286): every material image routed to its function, all in
 //       flight through the work queue (--serial: one after the other like the reference), and a
-//       <file>.textures.json manifest of what the .rsy image table holds; --dry-run prints it only.
-// Exit code 0 / EXIT_FAILURE like Packager.exe (src/Packager/Main.cpp:143-173).  Mesh import and the
-// .rsy writer stay in the reference's importer (they need fastgltf / MikkTSpace / meshoptimizer).
+//       <file>.textures.json manifest; --dry-run prints it only.
+//   rosy_packager_tex [--serial] [--dry-run] <file.fbx>        the image part of `Packager.exe <file.fbx>`
+//       (Main.cpp:67-124 -> Fbx.cpp:421-474): the *normal.tga / *mixmap.tga / *albedo.tga next to the .fbx.
+// Both asset routes then write <file>.rsy holding the asset's IMAGE TABLE exactly as asset::write stores it
+// (Asset.cpp:39-113 header + sizes, :296-340 image records; asset_images.h) - with --dry-run too, which needs
+// no GPU.  N1 ends there: materials, nodes and meshes are written by the reference's importers, which need
+// fastgltf / the FBX SDK / MikkTSpace / meshoptimizer (absent here) and are outside the texture stage.
+// Exit code 0 / EXIT_FAILURE like Packager.exe (src/Packager/Main.cpp:143-173).
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -16,6 +21,7 @@
 #include <fstream>
 #include <iostream>
 
+#include "asset_images.h"
 #include "gltf_images.h"
 #include "packager_texture.h"
 
@@ -42,15 +48,44 @@ int main(int argc, char** argv) {
             rosy_packager::gltf_image_plan plan;
             if (rosy_packager::plan_gltf_images(l, argv[i], plan, all_textures) != rosy::result::ok) return EXIT_FAILURE;
             const std::string manifest = rosy_packager::plan_to_json(plan);
+            // rosy_asset::asset::images: one per glTF image (Gltf.cpp:97-111), typed by the list that conditions it (:202-286)
+            std::vector<rosy_packager::asset_image> images;
+            for (const std::string& name : plan.image_names) images.push_back({rosy_packager::image_type_color, name});
+            for (const auto& job : plan.jobs)
+                if (job.image_index < images.size()) images[job.image_index].image_type = job.image_type;
+            std::filesystem::path rsy{argv[i]};
+            rsy.replace_extension(".rsy");  // Main.cpp:13-14
             if (dry_run) {
                 std::cout << manifest;
+                if (rosy_packager::write_rsy_image_table(l, rsy, images) != rosy::result::ok) return EXIT_FAILURE;
                 continue;
             }
             if (rosy_packager::condition_gltf_images(l, plan, serial) != rosy::result::ok) return EXIT_FAILURE;
             std::filesystem::path out{argv[i]};
             out.replace_extension(".textures.json");
             std::ofstream(out, std::ios::binary) << manifest;
+            if (rosy_packager::write_rsy_image_table(l, rsy, images) != rosy::result::ok) return EXIT_FAILURE;
             done += (int)plan.jobs.size();
+            continue;
+        }
+        if (std::filesystem::path(argv[i]).extension() == ".fbx") {
+            // Main.cpp:67-124 load_fbx, image part (Fbx.cpp:421-474)
+            std::filesystem::path rsy{argv[i]};
+            rsy.replace_extension(".rsy");
+            l->info(std::format("Parsing {} as {}", argv[i], rsy.string()));
+            std::vector<rosy_packager::fbx_image_job> jobs;
+            if (rosy_packager::plan_fbx_images(l, argv[i], jobs) != rosy::result::ok) return EXIT_FAILURE;
+            std::vector<rosy_packager::asset_image> images;
+            if (dry_run) {
+                for (const auto& job : jobs) {
+                    images.push_back({job.image_type, job.dds_path.string()});
+                    std::cout << job.image_type << " " << job.source_path.string() << " -> " << job.dds_path.string() << "\n";
+                }
+            } else if (rosy_packager::condition_fbx_images(l, jobs, serial, images) != rosy::result::ok) {
+                return EXIT_FAILURE;
+            }
+            if (rosy_packager::write_rsy_image_table(l, rsy, images) != rosy::result::ok) return EXIT_FAILURE;
+            done += (int)jobs.size();
             continue;
         }
         rosy::result r;

@@ -118,3 +118,105 @@ def test_gltf_packager_run(tmp_path, serial, tex, oracle):
         if oracle.have_ref_dds():
             info = oracle.ref_dds_read(dds.tobytes())
             assert info["format"] == 98 and info["numMips"] == 7
+
+
+# ---- .rsy image table (Asset.cpp:39-113, :296-340) and the FBX image routing (Fbx.cpp:421-474) -------------
+def _parse_rsy(data):
+    """hand-written reader of what asset::write stores for an asset that holds only images"""
+    import struct
+
+    magic, version, endian = struct.unpack_from("<III", data, 0)
+    coord = struct.unpack_from("<16f", data, 12)
+    (root_scene,) = struct.unpack_from("<I", data, 76)
+    sizes = struct.unpack_from("<6Q", data, 80)
+    off, images = 128, []
+    for _ in range(sizes[4]):
+        ntypes, nchars = struct.unpack_from("<QQ", data, off)
+        (itype,) = struct.unpack_from("<I", data, off + 16)
+        name = data[off + 20 : off + 20 + nchars].decode()
+        assert ntypes == 1
+        images.append((itype, name))
+        off += 20 + nchars
+    assert off == len(data), "trailing bytes"
+    return {"magic": magic, "version": version, "endianness": endian, "coord": coord, "root_scene": root_scene,
+            "sizes": sizes, "images": images}
+
+
+def test_rsy_image_table_bytes_for_gltf(tmp_path):
+    p, names = _write_gltf(tmp_path, with_images=False)
+    out = subprocess.run([CLI, "--dry-run", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    data = (tmp_path / "scene.rsy").read_bytes()
+    # hand-computed vector for the first bytes: 'RSYF' little endian, version 1, endianness 1, identity, root scene 0,
+    # sizes {0,0,0,0,4,0}
+    import struct
+
+    head = struct.pack("<III", 0x52535946, 1, 1) + struct.pack("<16f", *[1.0 if i % 5 == 0 else 0.0 for i in range(16)]) + \
+        struct.pack("<I", 0) + struct.pack("<6Q", 0, 0, 0, 0, 4, 0)
+    assert data[:128] == head and data[:4] == b"FYSR"
+    r = _parse_rsy(data)
+    # image i: name = <asset dir>/<uri up to the first '.'>.dds (Gltf.cpp:102-108); type from the list that conditions it:
+    # 0 colour (image 0), 2 metallic-roughness (image 1: the metallic list runs after the colour list), 1 normal (image 2),
+    # image 3 (emissive only) is never conditioned and keeps the default 0
+    want_names = [str(tmp_path / (n.replace(" ", "%20").split(".")[0] + ".dds")) for n in names]
+    assert [n for _, n in r["images"]] == want_names
+    assert [t for t, _ in r["images"]] == [0, 2, 1, 0]
+    # first record, byte for byte: size_t 1, size_t len, uint32 type, chars
+    n0 = want_names[0].encode()
+    assert data[128 : 148 + len(n0)] == struct.pack("<QQI", 1, len(n0), 0) + n0
+
+
+def _write_fbx_dir(tmp_path, size=64):
+    """a .fbx (never opened: the image section only scans its directory) and the TGA set of Fbx.cpp:426-430,
+    plus decoys: wrong extension, wrong suffix, suffix match inside the name only"""
+    from rosy_b200 import synth
+
+    def tga(path, img):
+        h, w = img.shape[:2]
+        hdr = bytes([0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, w & 255, w >> 8, h & 255, h >> 8, 32, 0x28])
+        path.write_bytes(hdr + img[..., [2, 1, 0, 3]].tobytes())
+
+    imgs = {"rock_normal.tga": synth.normal(size, size, 1), "rock_mixmap.tga": synth.make("metal_rough", size, size, 2),
+            "rock_albedo.tga": synth.albedo(size, size, 7), "albedo.tga": synth.albedo(size, size, 3)}
+    for n, im in imgs.items():
+        tga(tmp_path / n, im)
+    tga(tmp_path / "rock_height.tga", imgs["albedo.tga"])          # unsupported suffix
+    tga(tmp_path / "normal.tga.bak", imgs["albedo.tga"])           # not a .tga
+    (tmp_path / "rock_albedo.png").write_bytes(b"not read")        # FBX import only supports .tga
+    tga(tmp_path / "albedo_rock.tga", imgs["albedo.tga"])          # 'albedo' not at the end
+    (tmp_path / "rock.fbx").write_bytes(b"Kaydara FBX Binary  \x00")
+    return tmp_path / "rock.fbx", imgs
+
+
+def test_fbx_image_routing_plan_and_rsy(tmp_path):
+    fbx, imgs = _write_fbx_dir(tmp_path)
+    out = subprocess.run([CLI, "--dry-run", str(fbx)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    lines = [l for l in out.stdout.splitlines() if " -> " in l]
+    # visited in file-name order; type 0 albedo, 3 mixmap, 1 normal (Fbx.cpp:450,459,468)
+    want = [(0, "albedo.tga"), (0, "rock_albedo.tga"), (3, "rock_mixmap.tga"), (1, "rock_normal.tga")]
+    assert [(int(l.split()[0]), os.path.basename(l.split(" -> ")[0].split(" ", 1)[1])) for l in lines] == want
+    r = _parse_rsy((tmp_path / "rock.rsy").read_bytes())
+    assert r["sizes"] == (0, 0, 0, 0, 4, 0)
+    assert r["images"] == [(t, str(tmp_path / n.replace(".tga", ".dds"))) for t, n in want]
+    assert "image found:" in out.stdout + out.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("serial", [False, True])
+def test_fbx_packager_run(tmp_path, serial, tex):
+    """`rosy_packager_tex rock.fbx`: the three TGA kinds conditioned like Fbx.cpp:443-473, byte-checked against the
+    C ABI's single-texture entry points; a corrupt TGA aborts the asset (non-zero exit, reference error line)"""
+    fbx, imgs = _write_fbx_dir(tmp_path)
+    out = subprocess.run([CLI] + (["--serial"] if serial else []) + [str(fbx)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    for name, img in imgs.items():
+        kind = tex.KIND_NORMAL_MAP if name.endswith("normal.tga") else (tex.KIND_MIXMAP if name.endswith("mixmap.tga") else tex.KIND_COLOR)
+        got = np.fromfile(tmp_path / name.replace(".tga", ".dds"), dtype=np.uint8)
+        assert (got == tex.encode_rgba8(img, kind)).all(), name
+    assert not (tmp_path / "rock_height.dds").exists() and not (tmp_path / "albedo_rock.dds").exists()
+    assert len(_parse_rsy((tmp_path / "rock.rsy").read_bytes())["images"]) == 4
+    (tmp_path / "bad_normal.tga").write_bytes(b"\x00" * 10)
+    out = subprocess.run([CLI, "--serial", str(fbx)], capture_output=True, text=True)
+    assert out.returncode != 0
+    assert "error creating normal fbx image" in out.stdout + out.stderr
