@@ -6,8 +6,8 @@ the metric is quoted on; this tool fills in the table of DESIGN.md section 6 for
 
 Per configuration one JSON line: device-resident throughput (one batched call, CUDA events), end to
 end throughput through rosy_tex_submit_rgba8 / wait_all from pinned host buffers, and - with --psnr,
-on a 512x512 crop per texture kind - the PSNR of the GPU output next to the CPU oracle's (test
-infrastructure, used here only as the checker).
+on the FULL image of one texture per kind and size - the PSNR of the GPU output next to the CPU oracle's, per level and
+chain-weighted (test infrastructure, used here only as the checker).
 """
 import argparse
 import ctypes as C
@@ -137,24 +137,45 @@ def main():
                 "device_mpix_s": mpix / dev_ms * 1e3, "e2e_ms": e2e_ms, "e2e_mpix_s": mpix / e2e_ms * 1e3,
                 "e2e_equals_device": same}
         if args.psnr:
+            # PSNR delta: per level and chain-weighted, on the FULL image of one texture per kind and size
+            # (the oracle is the checker; it is never on the product path).  Each encoder is scored against the
+            # uncompressed level it was given (GPU and oracle chains differ by <= 1 LSB).
             import oracle as O
 
             ps = {}
             for img, d, k in texs:
-                if k in ps:
+                key = f"{k}-{img.shape[0]}"
+                if key in ps:
                     continue
-                crop = np.ascontiguousarray(img[:512, :512])
+                h, w = img.shape[:2]
                 okind = O.KIND_NORMAL if k == "normal" else O.KIND_SRGB
-                g = T.encode_rgba8(crop, d.kind, d.format, d.quality)
-                o = O.generate_texture(crop, okind, int(d.format), int(d.quality))
-                n0 = (512 // 4) ** 2 * (8 if d.format == T.FORMAT_BC4 else 16)
-                lvl0 = T.mips_rgba8(crop, d.kind)[0]
-                dg = O.decode_image(g[148:148 + n0], 512, 512, int(d.format))
-                do = O.decode_image(o[148:148 + n0], 512, 512, int(d.format))
-                ch = {T.FORMAT_BC7: 4, T.FORMAT_BC5: 2, T.FORMAT_BC4: 1}[int(d.format)]
-                ps[k] = {"gpu_db": float(O.psnr(lvl0, dg, ch)), "oracle_db": float(O.psnr(lvl0, do, ch)),
-                         "identical": bool((g == o).all())}
-            line["psnr_level0_512crop"] = ps
+                fmt, q = int(d.format), int(d.quality)
+                g = T.encode_rgba8(img, d.kind, d.format, d.quality)
+                o = O.generate_texture(img, okind, fmt, q)
+                chain_g, chain_o = T.mips_rgba8(img, d.kind), O.mip_chain(img, okind)
+                bb = 8 if fmt == T.FORMAT_BC4 else 16
+                ch = {T.FORMAT_BC7: 4, T.FORMAT_BC5: 2, T.FORMAT_BC4: 1}[fmt]
+                off, per_level, sg, so, npx, differing, nblk = 148, [], 0, 0, 0, 0, 0
+                for lg, lo in zip(chain_g, chain_o):
+                    lh, lw = lo.shape[:2]
+                    n = ((lw + 3) // 4) * ((lh + 3) // 4) * bb
+                    dg = lg[..., :ch].astype(np.int64) - O.decode_image(g[off:off + n], lw, lh, fmt)[..., :ch].astype(np.int64)
+                    do = lo[..., :ch].astype(np.int64) - O.decode_image(o[off:off + n], lw, lh, fmt)[..., :ch].astype(np.int64)
+                    eg, eo = int((dg * dg).sum()), int((do * do).sum())
+                    db = lambda e, m: 99.0 if e == 0 else float(10 * np.log10(255.0 ** 2 * m / e))
+                    per_level.append([round(db(eg, dg.size), 3), round(db(eo, do.size), 3)])
+                    sg, so, npx = sg + eg, so + eo, npx + dg.size
+                    differing += int((g[off:off + n].reshape(-1, bb) != o[off:off + n].reshape(-1, bb)).any(axis=1).sum())
+                    nblk += n // bb
+                    off += n
+                cg = 99.0 if sg == 0 else float(10 * np.log10(255.0 ** 2 * npx / sg))
+                co = 99.0 if so == 0 else float(10 * np.log10(255.0 ** 2 * npx / so))
+                ps[key] = {"chain_gpu_db": round(cg, 3), "chain_oracle_db": round(co, 3), "chain_delta_db": round(cg - co, 4),
+                           "per_level_gpu_oracle_db": per_level,
+                           "min_level_delta_db_levels_ge_32px": round(min(a - b for (a, b), l in zip(per_level, chain_o) if l.shape[0] * l.shape[1] >= 1024), 4),
+                           "blocks_differing_end_to_end": differing, "blocks": nblk,
+                           "max_mip_lsb": int(max(np.abs(a.astype(int) - b.astype(int)).max() for a, b in zip(chain_g, chain_o)))}
+            line["psnr_full_image"] = ps
         print(json.dumps(line), flush=True)
         del keep, flush
         torch.cuda.empty_cache()
