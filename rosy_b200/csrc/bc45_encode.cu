@@ -14,37 +14,15 @@
 
 #include <vector>
 
+#include "bc45_block.cuh"
 #include "tex_internal.h"
 
 namespace rosy_tex {
 namespace {
 
-constexpr int NT = 256;  // also the size of the reciprocal table
+using namespace bc45;
 
-// floor(2^20 / d) + 1 for d = 1..255 (0 for d = 0): exact reciprocals for quotients a / d with a * d < 2^20
-__device__ const uint32_t g_RECIP20[256] = {
-    0, 1048577, 524289, 349526, 262145, 209716, 174763, 149797, 131073, 116509, 104858, 95326,
-    87382, 80660, 74899, 69906, 65537, 61681, 58255, 55189, 52429, 49933, 47663, 45591,
-    43691, 41944, 40330, 38837, 37450, 36158, 34953, 33826, 32769, 31776, 30841, 29960,
-    29128, 28340, 27595, 26887, 26215, 25576, 24967, 24386, 23832, 23302, 22796, 22311,
-    21846, 21400, 20972, 20561, 20165, 19785, 19419, 19066, 18725, 18397, 18079, 17773,
-    17477, 17190, 16913, 16645, 16385, 16132, 15888, 15651, 15421, 15197, 14980, 14769,
-    14564, 14365, 14170, 13982, 13798, 13618, 13444, 13274, 13108, 12946, 12788, 12634,
-    12484, 12337, 12193, 12053, 11916, 11782, 11651, 11523, 11398, 11276, 11156, 11038,
-    10923, 10811, 10700, 10592, 10486, 10382, 10281, 10181, 10083, 9987, 9893, 9800,
-    9710, 9620, 9533, 9447, 9363, 9280, 9199, 9119, 9040, 8963, 8887, 8812,
-    8739, 8666, 8595, 8526, 8457, 8389, 8323, 8257, 8193, 8129, 8066, 8005,
-    7944, 7885, 7826, 7768, 7711, 7654, 7599, 7544, 7490, 7437, 7385, 7333,
-    7282, 7232, 7183, 7134, 7085, 7038, 6991, 6945, 6899, 6854, 6809, 6766,
-    6722, 6679, 6637, 6595, 6554, 6513, 6473, 6433, 6394, 6356, 6317, 6279,
-    6242, 6205, 6169, 6133, 6097, 6062, 6027, 5992, 5958, 5925, 5891, 5858,
-    5826, 5794, 5762, 5730, 5699, 5668, 5638, 5608, 5578, 5549, 5519, 5490,
-    5462, 5434, 5406, 5378, 5350, 5323, 5296, 5270, 5243, 5217, 5191, 5166,
-    5141, 5116, 5091, 5066, 5042, 5018, 4994, 4970, 4947, 4923, 4900, 4878,
-    4855, 4833, 4810, 4789, 4767, 4745, 4724, 4703, 4682, 4661, 4640, 4620,
-    4600, 4579, 4560, 4540, 4520, 4501, 4482, 4463, 4444, 4425, 4406, 4388,
-    4370, 4351, 4333, 4316, 4298, 4280, 4263, 4246, 4229, 4212, 4195, 4178,
-    4162, 4145, 4129, 4113};
+constexpr int NT = 256;  // also the size of the reciprocal table
 
 struct Params {
     Chain chain;
@@ -54,63 +32,6 @@ struct Params {
     int first_level, num_levels;
     uint64_t first_block, num_blocks;
 };
-
-// 16 samples packed 4 per word (texel 4k+j in byte j of v[k]) -> 8-byte alpha-style block.
-//
-// stb__CompressAlphaBlock picks, per sample, ind = floor(a / dist) by three compare-and-subtract
-// steps (a = 7 v + bias, 0 <= a < 8 dist) and maps it to the block's index order
-// {1,7,6,5,4,3,2,0}[ind].  The same integers are produced here with far fewer instructions (the
-// kernel has to encode at HBM speed): the quotient is one multiply by the exact 20-bit reciprocal
-// recip[dist] = floor(2^20 / dist) + 1 (exact because a * dist < 2^20), the sixteen 3-bit quotients
-// are gathered as nibbles of two words, and the index map and the 4-bit -> 3-bit packing are done on
-// eight samples at a time with word-wide logic.
-__device__ __forceinline__ uint32_t map_and_pack8(uint32_t x /* eight quotients, one per nibble */) {
-    // {1,7,6,5,4,3,2,0}[q] = ((8 - q) & 7) ^ (1 if the result is 0 or 1)
-    uint32_t r = (0x88888888u - x) & 0x77777777u;
-    r ^= ~((r >> 1) | (r >> 2)) & 0x11111111u;
-    // nibbles -> 3-bit fields: pairs, then quads, then all eight (24 bits)
-    uint32_t t = (r & 0x07070707u) | ((r >> 1) & 0x38383838u);
-    t = (t & 0x003F003Fu) | ((t >> 2) & 0x0FC00FC0u);
-    return (t & 0x00000FFFu) | ((t >> 4) & 0x00FFF000u);
-}
-
-__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c) {
-    uint32_t d;  // kept opaque so that the compiler does not re-factor the folded constants back into three multiplies
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-
-__device__ __forceinline__ uint2 alpha_block(const uint32_t v[4], const uint32_t* recip) {
-    // the sixteen samples as integers (needed for the multiplies anyway), min / max by 3-input min / max
-    // (stb's `else if` update gives the same mn/mx: a sample that lowers mn can never also raise mx past
-    // the first sample)
-    int sv[16];
-#pragma unroll
-    for (int i = 0; i < 16; i++) sv[i] = (int)__byte_perm(v[i >> 2], 0u, 0x4440 + (i & 3));
-    int mn = sv[0], mx = sv[0];
-#pragma unroll
-    for (int i = 1; i < 15; i += 2) {
-        mn = __vimin3_s32(mn, sv[i], sv[i + 1]);
-        mx = __vimax3_s32(mx, sv[i], sv[i + 1]);
-    }
-    mn = min(mn, sv[15]);
-    mx = max(mx, sv[15]);
-    const int dist = mx - mn;
-    int bias = dist < 8 ? dist - 1 : dist / 2 + 2;
-    bias -= mn * 7;
-    const uint32_t M = recip[dist];  // 0 for dist == 0: every quotient is 0, as in stb (a = -1 fails every compare)
-    const uint32_t M7 = 7u * M, biasM = (uint32_t)(bias * (int)M);
-    uint32_t nib[2] = {0u, 0u};
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t t = mad_u32((uint32_t)sv[i], M7, biasM);  // (7 s + bias) * M, below 2^24
-        const int j = i & 7, sh = 20 - 4 * j;
-        nib[i >> 3] |= (sh >= 0 ? t >> sh : t << -sh) & (7u << (4 * j));
-    }
-    const uint32_t lo = map_and_pack8(nib[0]), hi = map_and_pack8(nib[1]);  // 24 bits each
-    // block = mx, mn, then 48 index bits
-    return make_uint2((uint32_t)mx | ((uint32_t)mn << 8) | (lo << 16), (lo >> 16) | (hi << 8));
-}
 
 // One texture (P1, plist == nullptr) or a batch: plist[t] describes texture t, whose blocks are
 // threads base_of[t] .. base_of[t+1]-1 of the launch.
@@ -164,15 +85,8 @@ bc45_encode_kernel(const __grid_constant__ Params P1, const Params* __restrict__
                     __ldg(reinterpret_cast<const uint32_t*>(base) + (uint64_t)sy * lv.w + sx);
             }
     }
-    // byte-planar R (and G): texel 4k+j -> byte j of word k
     uint32_t r4[4], g4[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t t0 = __byte_perm(px[4 * k], px[4 * k + 1], 0x5140);
-        const uint32_t t1 = __byte_perm(px[4 * k + 2], px[4 * k + 3], 0x5140);
-        r4[k] = __byte_perm(t0, t1, 0x5410);
-        g4[k] = __byte_perm(t0, t1, 0x7632);
-    }
+    planes_rg(px, r4, g4);
     const uint2 rb = alpha_block(r4, recip);
     if (BC5) {
         const uint2 gbk = alpha_block(g4, recip);
@@ -232,7 +146,9 @@ int launch_bc45_batch(int n, const Bc45BatchItem* items, void* d_desc, cudaStrea
         for (int i = 0; i < n; i++) {
             if (items[i].bc5 != bc5) continue;
             Params P;
-            fill_params(P, items[i].chain, 0, items[i].chain.levels, bc5, items[i].d_level0, items[i].d_chain, items[i].d_blocks);
+            const int fl = items[i].first_level;  // levels below it were encoded by the fused mip kernel
+            if (fl >= items[i].chain.levels) continue;
+            fill_params(P, items[i].chain, fl, items[i].chain.levels - fl, bc5, items[i].d_level0, items[i].d_chain, items[i].d_blocks);
             base.push_back(total);
             total += P.num_blocks;
             ps.push_back(P);

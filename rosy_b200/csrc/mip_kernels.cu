@@ -36,6 +36,7 @@
 #include <mutex>
 #include <vector>
 
+#include "bc45_block.cuh"
 #include "tex_internal.h"
 
 namespace rosy_tex {
@@ -189,6 +190,7 @@ constexpr int INFO_RING = 16;        // >= STAGES + L3_BUFS + 1 tile descriptors
 constexpr int TAIL_QUEUE = 64;
 constexpr int TILE_BYTES = TILE * TILE * 4;
 constexpr int TAIL_SMEM_PX = 128;  // tail levels with at most this many texels are reduced in shared memory
+constexpr int FUSED_ENC_LEVELS = 5;  // fused mip + BC5 / BC4 encode: levels 0..4 of a 64x64 tile are whole 4x4 blocks
 
 // Colour values travel through the fused kernel BIASED: a working value is c' = c + SRGB_BIAS
 // (premultiplied: P' = P + SRGB_BIAS * A), which every box average preserves because its weights
@@ -227,6 +229,9 @@ struct alignas(64) MipTex {
     int levels;
     int normalize;
     int pad;
+    uint8_t* blocks;       // fused encode (ENC != 0): the texture's block stream; levels 0..4 are encoded here
+    uint32_t lblk[FUSED_ENC_LEVELS];  // first block of levels 0..4 in that stream
+    uint32_t pad2;
     uint32_t lw[ROSY_TEX_MAX_LEVELS], lh[ROSY_TEX_MAX_LEVELS];
     uint64_t lpx[ROSY_TEX_MAX_LEVELS];  // px_offset per level
 };
@@ -242,6 +247,8 @@ struct TileInfo {
     int normalize;
     uint32_t off[8];  // pixel offset of levels 0..6 in the chain buffer (fits 32 bits up to 32768^2)
     uint32_t org[4];  // pixel index of this tile's first texel in levels 0..3 (off[l] included)
+    uint8_t* blocks;  // fused encode: the block stream and the index of this tile's first block in levels 0..4
+    uint32_t borg[FUSED_ENC_LEVELS];
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -500,17 +507,57 @@ struct GroupSmem {
     int queue[TAIL_QUEUE];        // textures whose last tile this group finished
     int nqueue;
 };
+// fused encode only: lives in the gap between group 0's GroupSmem and the 64 KB boundary
+struct EncSmem {
+    uint32_t recip[256];                   // bc45::g_RECIP20
+    uint16_t l2rg[GROUPS][L3_BUFS][256];   // R | G << 8 of the consumers' level-2 texels, one per consumer thread
+    uint16_t l34rg[GROUPS][96];            // the auxiliary warp's level-3 (8x8) and level-4 (4x4) texels of the current tile
+};
 constexpr uint32_t SMEM_WINDOW_BASE = 0x400;  // dynamic shared memory starts 1 KB into the CTA's window (checked in the kernel)
 constexpr size_t SRGB_TAB_BYTES = ((SRGB_ENTRIES + 2) * sizeof(float2) + 127) / 128 * 128;
 constexpr size_t TAIL_BYTES = 2 * TAIL_SMEM_PX * sizeof(float4);  // per group, after the encode table
 constexpr size_t L2_RING_BYTES = (size_t)L3_BUFS * 256 * sizeof(float4);  // per group: level-2 values of a tile, one per consumer thread
 constexpr size_t FUSED_SMEM_BYTES =
     (0x10000 - SMEM_WINDOW_BASE) + LIN_BYTES + sizeof(GroupSmem) + SRGB_TAB_BYTES + GROUPS * (TAIL_BYTES + L2_RING_BYTES);
-static_assert(sizeof(GroupSmem) <= 0x10000 - SMEM_WINDOW_BASE, "group 0 must fit below the 64 KB boundary");
+static_assert(sizeof(GroupSmem) + sizeof(EncSmem) <= 0x10000 - SMEM_WINDOW_BASE, "group 0 and the encode staging must fit below the 64 KB boundary");
 static_assert(FUSED_SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// ---- fused encode helpers (ENC 1: BC5 from bytes 0 and 1 of the RGBA8 texels, ENC 2: BC4 from byte 0) ----
+// one thread holds the whole block (row major)
+template <int ENC>
+__device__ __forceinline__ void encode_own_block(const uint32_t px[16], const uint32_t* recip, uint8_t* blocks, uint32_t bi) {
+    uint32_t r4[4], g4[4];
+    bc45::planes_rg(px, r4, g4);
+    const uint2 rblk = bc45::alpha_block(r4, recip);
+    if (ENC == 1) {
+        const uint2 gblk = bc45::alpha_block(g4, recip);
+        *reinterpret_cast<uint4*>(blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
+    } else {
+        *reinterpret_cast<uint2*>(blocks + (size_t)bi * 8) = rblk;
+    }
+}
+// four lanes hold the block, a 2x2 quad each (w[row][col]); every lane stores one 32-bit word of it
+template <int ENC>
+__device__ __forceinline__ void encode_quad_block(const uint32_t w[2][2], const uint32_t* recip, uint32_t qmask, int dx, int dy,
+                                                  uint8_t* blocks, uint32_t bi) {
+    const int q = dx | (dy << 1);
+    int s[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) s[i] = (int)(w[i >> 1][i & 1] & 255u);
+    const uint2 rblk = bc45::alpha_block_quad(s, recip, qmask, dx, dy);
+    if (ENC == 1) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[i] = (int)((w[i >> 1][i & 1] >> 8) & 255u);
+        const uint2 gblk = bc45::alpha_block_quad(s, recip, qmask, dx, dy);
+        const uint32_t word = q == 0 ? rblk.x : (q == 1 ? rblk.y : (q == 2 ? gblk.x : gblk.y));
+        reinterpret_cast<uint32_t*>(blocks + (size_t)bi * 16)[q] = word;
+    } else if (dy == 0) {
+        reinterpret_cast<uint32_t*>(blocks + (size_t)bi * 8)[q] = dx ? rblk.y : rblk.x;
+    }
 }
 
 // Two independent groups of 10 warps per CTA; roles inside a group (no CTA-wide barrier anywhere in
@@ -520,7 +567,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //              completion tickets; textures whose last tile it saw are queued for the tail
 //   warp  9    producer: one lane issues the TMA loads, STAGES tiles ahead
 // After the loop the consumers reduce the queued textures' level-6 images down to 1x1.
-template <bool NORMAL>
+//
+// ENC != 0 (1: BC5 from R,G; 2: BC4 from R): the tile's levels 0..4 are whole 4x4 blocks and are encoded here instead
+// of being written to the chain buffer (SURVEY 8d's fused floor: 4 N bytes read, 4 N / 3 bytes of blocks written):
+//   level 0   one block per consumer thread (its 4x4 patch)
+//   level 1   one block per four lanes {l, l^1, l^16, l^17}, combined with redux.sync (bc45::alpha_block_quad)
+//   level 2-4 16 + 4 + 1 blocks per tile by lanes 0..20 of the auxiliary warp, from texels staged in shared memory
+// Levels 5.. go to the chain buffer as before and are encoded by a small bc45_encode_kernel launch.
+template <bool NORMAL, int ENC>
 __global__ void __launch_bounds__(NTHREADS_TOTAL * GROUPS, 1)
 mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict__ texs,
                  const int* __restrict__ tile_base, int ntex, int total_tiles) {
@@ -538,6 +592,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     }
     uint8_t* const lin_raw = smem_raw + (0x10000 - SMEM_WINDOW_BASE);
     GroupSmem& S = *reinterpret_cast<GroupSmem*>(grp ? lin_raw + LIN_BYTES : smem_raw);
+    EncSmem& E = *reinterpret_cast<EncSmem*>(smem_raw + sizeof(GroupSmem));
+    constexpr int BB = ENC == 2 ? 8 : 16;  // bytes per block
     float* const lin_tab = reinterpret_cast<float*>(lin_raw);
     float2* const srgb_tab = reinterpret_cast<float2*>(lin_raw + LIN_BYTES + sizeof(GroupSmem));
     const float2* tab = srgb_tab - SRGB_BASE;
@@ -561,6 +617,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         }
         for (int i = threadIdx.x; i < SRGB_ENTRIES; i += NTHREADS_TOTAL * GROUPS) srgb_tab[i] = c_SRGB_ENCODE[i];
     }
+    if (ENC && threadIdx.x < 256) E.recip[threadIdx.x] = bc45::g_RECIP20[threadIdx.x];
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
             mbar_init(&S.full[s], 1);
@@ -587,6 +644,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         uint32_t t_w = 0, t_off[7] = {0, 0, 0, 0, 0, 0, 0};
         uint8_t* t_chain = nullptr;
         float4* t_top = nullptr;
+        uint8_t* t_blocks = nullptr;
+        uint32_t t_lblk[FUSED_ENC_LEVELS] = {0, 0, 0, 0, 0};
         for (int it = 0; it < my_tiles; it++) {
             const int t = first_tile + it;
             const int s = it % STAGES;
@@ -607,6 +666,11 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 t_top = T->levels > 7 ? T->tile_top : nullptr;
 #pragma unroll
                 for (int l = 0; l < 7; l++) t_off[l] = (uint32_t)T->lpx[l];
+                if (ENC) {
+                    t_blocks = T->blocks;
+#pragma unroll
+                    for (int l = 0; l < FUSED_ENC_LEVELS; l++) t_lblk[l] = T->lblk[l];
+                }
             }
             const int lt = t - t_base;
             const int tile_x = lt % t_tiles_x, tile_y = lt / t_tiles_x;
@@ -626,6 +690,12 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 #pragma unroll
             for (int l = 0; l < 4; l++)
                 I.org[l] = t_off[l] + (uint32_t)(tile_y * (TILE >> l)) * (t_w >> l) + (uint32_t)(tile_x * (TILE >> l));
+            if (ENC) {
+                I.blocks = t_blocks;
+#pragma unroll
+                for (int l = 0; l < FUSED_ENC_LEVELS; l++)  // level l: (16 >> l)^2 blocks per tile, t_w >> (2 + l) blocks per row
+                    I.borg[l] = t_lblk[l] + (uint32_t)(tile_y * (16 >> l)) * (t_w >> (2 + l)) + (uint32_t)(tile_x * (16 >> l));
+            }
             mbar_expect_tx(&S.full[s], TILE_BYTES);  // release: the descriptor above is visible to the waiters
         }
         return;
@@ -666,6 +736,19 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             uint32_t* c3b = c3a + 4 * w3;
             uint32_t px3a, px3b, pxc;
             float4 v6;
+            // fused encode: rows of the lane's block as R | G << 8 per texel, two words per row.  Lanes 0..15 take the
+            // sixteen level-2 blocks of the tile here, before the level-2 buffer is released.
+            uint32_t eb[8];
+            if (ENC) {
+                const uint2* src = reinterpret_cast<const uint2*>(E.l2rg[grp][b]);
+                const int bx2 = lane & 3, by2 = (lane >> 2) & 3;
+#pragma unroll
+                for (int y = 0; y < 4; y++) {
+                    const uint2 v = src[(4 * by2 + y) * 4 + bx2];
+                    eb[2 * y] = v.x;
+                    eb[2 * y + 1] = v.y;
+                }
+            }
             if (!NORMAL) {
                 const float4* qa = l2ring + b * 256 + (2 * Ya) * 16 + 2 * X;  // level-3 rows Ya and Ya + 4
                 const float4* qb = qa + 8 * 16;
@@ -713,11 +796,59 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 pxc = role == 4 ? p4 : pf;
             }
             const bool has_tail = I.tile_top != nullptr;
-            *c3a = px3a;
-            *c3b = px3b;
-            if (role == 4)
-                chain32[I.off[4] + (size_t)(I.tile_y * 4 + (Ya >> 1) + (useB ? 2 : 0)) * w4 + I.tile_x * 4 + (X >> 1)] = pxc;
-            else if (role == 5)
+            if (ENC) {
+                uint16_t* L = E.l34rg[grp];
+                L[Ya * 8 + X] = (uint16_t)px3a;
+                L[(Ya + 4) * 8 + X] = (uint16_t)px3b;
+                if (role == 4) L[64 + ((Ya >> 1) + (useB ? 2 : 0)) * 4 + (X >> 1)] = (uint16_t)pxc;
+                __syncwarp();
+                const uint2* L2 = reinterpret_cast<const uint2*>(L);
+                if (lane >= 16 && lane < 20) {  // the four level-3 blocks
+                    const int bx3 = lane & 1, by3 = (lane >> 1) & 1;
+#pragma unroll
+                    for (int y = 0; y < 4; y++) {
+                        const uint2 v = L2[(4 * by3 + y) * 2 + bx3];
+                        eb[2 * y] = v.x;
+                        eb[2 * y + 1] = v.y;
+                    }
+                } else if (lane == 20) {  // the level-4 block
+#pragma unroll
+                    for (int y = 0; y < 4; y++) {
+                        const uint2 v = L2[16 + y];
+                        eb[2 * y] = v.x;
+                        eb[2 * y + 1] = v.y;
+                    }
+                }
+                __syncwarp();  // the staging buffer is rewritten for the next tile
+                if (lane < 21) {
+                    uint32_t r4[4], g4[4];
+#pragma unroll
+                    for (int y = 0; y < 4; y++) {
+                        r4[y] = __byte_perm(eb[2 * y], eb[2 * y + 1], 0x6420);
+                        g4[y] = __byte_perm(eb[2 * y], eb[2 * y + 1], 0x7531);
+                    }
+                    uint32_t bi;  // block index in the texture's stream
+                    if (lane < 16)
+                        bi = I.borg[2] + (uint32_t)((lane >> 2) & 3) * w4 + (uint32_t)(lane & 3);
+                    else if (lane < 20)
+                        bi = I.borg[3] + (uint32_t)((lane >> 1) & 1) * w5 + (uint32_t)(lane & 1);
+                    else
+                        bi = I.borg[4];
+                    const uint2 rblk = bc45::alpha_block(r4, E.recip);
+                    if (ENC == 1) {
+                        const uint2 gblk = bc45::alpha_block(g4, E.recip);
+                        *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
+                    } else {
+                        *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
+                    }
+                }
+            } else {
+                *c3a = px3a;
+                *c3b = px3b;
+            }
+            if (role == 4) {
+                if (!ENC) chain32[I.off[4] + (size_t)(I.tile_y * 4 + (Ya >> 1) + (useB ? 2 : 0)) * w4 + I.tile_x * 4 + (X >> 1)] = pxc;
+            } else if (role == 5)
                 chain32[I.off[5] + (size_t)(I.tile_y * 2 + (useB ? 1 : 0)) * w5 + I.tile_x * 2 + (X >> 2)] = pxc;
             else if (role == 6) {
                 chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = pxc;
@@ -780,9 +911,14 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.empty[s]);  // the texels are in registers: the stage may be refilled
         const int b = it % L3_BUFS;
+        // fused encode: the level-1 texels of this thread (2x2) and its level-2 texel, as the chain would hold them
+        uint32_t l1w[2][2], px2 = 0u;
+        const uint32_t qmask = 0x00030003u << (lane & 0x0E);  // the four lanes that share a level-1 block
+        const int qdx = lane & 1, qdy = (lane >> 4) & 1;
 
         if (NORMAL) {
             // level 0 of a normal map is the re-normalised input (Packager.cpp:294-296 at mip 0)
+            uint32_t blk0[16];
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 uint4 o = rows[r];
@@ -792,8 +928,16 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                     o.z = normalize_texel(o.z);
                     o.w = normalize_texel(o.w);
                 }
-                c0[(size_t)r * (w0 / 4)] = o;
+                if (ENC) {
+                    blk0[4 * r + 0] = o.x;
+                    blk0[4 * r + 1] = o.y;
+                    blk0[4 * r + 2] = o.z;
+                    blk0[4 * r + 3] = o.w;
+                } else {
+                    c0[(size_t)r * (w0 / 4)] = o;
+                }
             }
+            if (ENC) encode_own_block<ENC>(blk0, E.recip, I.blocks, I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx);
             // exact integer channel sums, two 16-bit lanes per word
             uint32_t rb2 = 0, ga2 = 0;
 #pragma unroll
@@ -805,15 +949,26 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 const uint32_t rb_r = (a.z & 0x00FF00FFu) + (a.w & 0x00FF00FFu) + (bq.z & 0x00FF00FFu) + (bq.w & 0x00FF00FFu);
                 const uint32_t ga_r = ((a.z >> 8) & 0x00FF00FFu) + ((a.w >> 8) & 0x00FF00FFu) +
                                       ((bq.z >> 8) & 0x00FF00FFu) + ((bq.w >> 8) & 0x00FF00FFu);
-                *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
-                    make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
+                const uint2 o1 = make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
+                if (ENC) {
+                    l1w[j][0] = o1.x;
+                    l1w[j][1] = o1.y;
+                } else {
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = o1;
+                }
                 rb2 += rb_l + rb_r;
                 ga2 += ga_l + ga_r;
             }
-            *c2 = finish_normal_sums<2>(rb2, ga2, normalize);
+            px2 = finish_normal_sums<2>(rb2, ga2, normalize);
+            if (!ENC) *c2 = px2;
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
             reinterpret_cast<uint2*>(l2ring + b * 256)[tid] = make_uint2(rb2, ga2);
         } else {
+            if (ENC) {  // colour maps: level 0 is the input itself (Packager.cpp:245 at mip 0)
+                const uint32_t blk0[16] = {rows[0].x, rows[0].y, rows[0].z, rows[0].w, rows[1].x, rows[1].y, rows[1].z, rows[1].w,
+                                           rows[2].x, rows[2].y, rows[2].z, rows[2].w, rows[3].x, rows[3].y, rows[3].z, rows[3].w};
+                encode_own_block<ENC>(blk0, E.recip, I.blocks, I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx);
+            }
             uint32_t all = rows[0].x & rows[0].y & rows[0].z & rows[0].w;
 #pragma unroll
             for (int r = 1; r < 4; r++) all &= rows[r].x & rows[r].y & rows[r].z & rows[r].w;
@@ -838,10 +993,16 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                         srg = add2(srg, rg);
                         sb += b_;
                     }
-                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    if (ENC) {
+                        l1w[j][0] = o[0];
+                        l1w[j][1] = o[1];
+                    } else {
+                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    }
                 }
                 v2 = make_float4(srg.x * 0.25f, srg.y * 0.25f, sb * 0.25f, 1.0f);
-                *c2 = finish_opaque(v2.x, v2.y, v2.z, tab);
+                px2 = finish_opaque(v2.x, v2.y, v2.z, tab);
+                if (!ENC) *c2 = px2;
             } else {
                 float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -864,14 +1025,26 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                         o[i] = finish_colour(q, tab);
                         sum = add4(sum, q);
                     }
-                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    if (ENC) {
+                        l1w[j][0] = o[0];
+                        l1w[j][1] = o[1];
+                    } else {
+                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    }
                 }
                 v2 = scale4(sum, 0.25f);
-                *c2 = finish_colour(v2, tab);
+                px2 = finish_colour(v2, tab);
+                if (!ENC) *c2 = px2;
             }
             // levels 3.. are the auxiliary warp's: hand over this thread's level-2 value
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
             l2ring[b * 256 + tid] = v2;
+        }
+        if (ENC) {
+            // the l3empty wait above also covers the level-2 texel buffer
+            E.l2rg[grp][b][tid] = (uint16_t)px2;
+            // level 1: one block per four lanes
+            encode_quad_block<ENC>(l1w, E.recip, qmask, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.l3full[b]);
@@ -940,7 +1113,7 @@ int force_generic() {
 
 // describe one texture for the fused kernel; false if the tensor map cannot be built
 bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba, uint8_t* d_chain,
-                 void* d_scratch, int tile_base) {
+                 void* d_scratch, int tile_base, uint8_t* d_blocks = nullptr) {
     memset(&T, 0, sizeof T);
     const cuuint64_t dims[2] = {c.lv[0].w, c.lv[0].h};
     const cuuint64_t strides[1] = {(cuuint64_t)c.lv[0].w * 4};
@@ -964,6 +1137,8 @@ bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba
     T.tile_top = reinterpret_cast<float4*>(sc + 256);
     T.tail_a = T.tile_top + ntiles;
     T.tail_b = T.tail_a + ntiles;
+    T.blocks = d_blocks;
+    for (int l = 0; l < FUSED_ENC_LEVELS && l < c.levels; l++) T.lblk[l] = (uint32_t)c.lv[l].blk_offset;
     for (int l = 0; l < c.levels; l++) {
         T.lw[l] = c.lv[l].w;
         T.lh[l] = c.lv[l].h;
@@ -972,22 +1147,43 @@ bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba
     return true;
 }
 
-template <bool NORMAL>
-cudaError_t launch_fused(const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
+template <bool NORMAL, int ENC>
+cudaError_t launch_fused_t(const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
                          int total_tiles, cudaStream_t s) {
     // function attributes are per device: set once on each device that launches
     static std::once_flag once[64];
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     std::call_once(once[dev & 63], [] {
-        cudaFuncSetAttribute(mip_fused_kernel<NORMAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(mip_fused_kernel<NORMAL, ENC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)FUSED_SMEM_BYTES);
     });
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int want = (total_tiles + GROUPS - 1) / GROUPS;  // every group of every CTA gets a tile
     const int grid = want < sms ? want : sms;
-    mip_fused_kernel<NORMAL><<<grid, NTHREADS_TOTAL * GROUPS, FUSED_SMEM_BYTES, s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
+    mip_fused_kernel<NORMAL, ENC><<<grid, NTHREADS_TOTAL * GROUPS, FUSED_SMEM_BYTES, s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
     return cudaGetLastError();
+}
+// enc: 0 mips only, 1 mips + BC5 of levels 0..4, 2 mips + BC4 of levels 0..4
+cudaError_t launch_fused(bool normal, int enc, const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
+                         int total_tiles, cudaStream_t s) {
+    if (normal) {
+        if (enc == 1) return launch_fused_t<true, 1>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+        if (enc == 2) return launch_fused_t<true, 2>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+        return launch_fused_t<true, 0>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+    }
+    if (enc == 1) return launch_fused_t<false, 1>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+    if (enc == 2) return launch_fused_t<false, 2>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+    return launch_fused_t<false, 0>(single, d_texs, d_tile_base, ntex, total_tiles, s);
+}
+
+int fuse_encode_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ROSY_TEX_FUSE_ENCODE");  // 0: mips and BC5 / BC4 blocks always as separate launches
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v;
 }
 
 }  // namespace
@@ -1013,7 +1209,8 @@ size_t mips_scratch_bytes(const Chain& c) {
 // two kinds (colour, normal) may be present: each has its own descriptor array and tile-base array, each
 // 256-byte aligned, so the worst case carries one extra alignment gap per array and two extra ints
 size_t mips_batch_desc_bytes(int n) {
-    return align256((size_t)n * sizeof(MipTex)) + 256 + align256((size_t)(n + 2) * sizeof(int)) + 256;
+    // up to six launches (two kinds x {mips only, + BC5, + BC4}), each with its own 256-byte aligned arrays
+    return align256((size_t)n * sizeof(MipTex)) + 6 * 256 + align256((size_t)(n + 6) * sizeof(int)) + 6 * 256;
 }
 
 int mips_upload_tables() {
@@ -1124,15 +1321,21 @@ static int launch_mips_generic(const Chain& c, bool normal_map, int normalize, c
     return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
 
+// Levels 0 .. mips_fused_encode_levels() - 1 of a BC5 / BC4 texture are encoded by the fused mip kernel itself when the
+// launch below is given the block stream; 0: the texture takes separate mip and encode launches.
+int mips_fused_encode_levels(const Chain& c, int format) {
+    const bool bc45 = format == ROSY_TEX_FORMAT_BC5 || format == ROSY_TEX_FORMAT_BC4;
+    return bc45 && fuse_encode_enabled() && fused_ok(c) && !force_generic() && get_encode_tiled() ? FUSED_ENC_LEVELS : 0;
+}
+
 int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
-                uint8_t* d_chain, void* d_scratch, cudaStream_t s) {
+                uint8_t* d_chain, void* d_scratch, cudaStream_t s, int enc_format, uint8_t* d_blocks) {
     if (fused_ok(c) && !force_generic() && get_encode_tiled()) {
+        const int enc = d_blocks && mips_fused_encode_levels(c, enc_format) ? (enc_format == ROSY_TEX_FORMAT_BC5 ? 1 : 2) : 0;
         MipTex T;
-        if (!fill_miptex(T, c, normalize, d_rgba, d_chain, d_scratch, 0)) return -1;
+        if (!fill_miptex(T, c, normalize, d_rgba, d_chain, d_scratch, 0, enc ? d_blocks : nullptr)) return -1;
         const int ntiles = T.tiles_x * T.tiles_y;
-        const cudaError_t e = normal_map ? launch_fused<true>(&T, nullptr, nullptr, 1, ntiles, s)
-                                         : launch_fused<false>(&T, nullptr, nullptr, 1, ntiles, s);
-        return e == cudaSuccess ? 1 : -1;
+        return launch_fused(normal_map, enc, &T, nullptr, nullptr, 1, ntiles, s) == cudaSuccess ? 1 : -1;
     }
     return launch_mips_generic(c, normal_map, normalize, d_rgba, d_chain, d_scratch, s);
 }
@@ -1146,7 +1349,8 @@ int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream
     std::vector<int> base;
     uint8_t* dd = reinterpret_cast<uint8_t*>(d_desc);
     size_t used = 0;  // descriptors of the two kinds sit one after the other in d_desc
-    for (int kind = 0; kind < 2; kind++) {
+    for (int group = 0; group < 6; group++) {
+        const int kind = group & 1, enc = group >> 1;
         texs.clear();
         base.clear();
         int total = 0;
@@ -1154,8 +1358,10 @@ int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream
             const MipBatchItem& it = items[i];
             if ((int)it.normal_map != kind) continue;
             if (!(fused_ok(it.chain) && !force_generic() && get_encode_tiled())) continue;
+            const int it_enc = it.d_blocks && mips_fused_encode_levels(it.chain, it.enc_format) ? (it.enc_format == ROSY_TEX_FORMAT_BC5 ? 1 : 2) : 0;
+            if (it_enc != enc) continue;
             MipTex T;
-            if (!fill_miptex(T, it.chain, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, total)) return -1;
+            if (!fill_miptex(T, it.chain, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, total, enc ? it.d_blocks : nullptr)) return -1;
             base.push_back(total);
             total += T.tiles_x * T.tiles_y;
             texs.push_back(T);
@@ -1169,9 +1375,7 @@ int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream
         if (cudaMemcpyAsync(d_texs, texs.data(), texs.size() * sizeof(MipTex), cudaMemcpyHostToDevice, s) != cudaSuccess ||
             cudaMemcpyAsync(d_base, base.data(), base.size() * sizeof(int), cudaMemcpyHostToDevice, s) != cudaSuccess)
             return -1;
-        const cudaError_t e = kind ? launch_fused<true>(&texs[0], d_texs, d_base, (int)texs.size(), total, s)
-                                   : launch_fused<false>(&texs[0], d_texs, d_base, (int)texs.size(), total, s);
-        if (e != cudaSuccess) return -1;
+        if (launch_fused(kind != 0, enc, &texs[0], d_texs, d_base, (int)texs.size(), total, s) != cudaSuccess) return -1;
         launches++;
     }
     for (int i = 0; i < n; i++) {

@@ -320,8 +320,12 @@ int grow(uint8_t*& p, size_t& cap, size_t need) {
 
 int encode_on_stream(const Chain& c, const Resolved& r, const uint8_t* d_rgba, uint8_t* d_chain, void* d_scratch,
                      uint8_t* d_blocks, cudaStream_t stream, bool do_mips, bool do_blocks) {
+    // BC5 / BC4 with both stages: the fused mip kernel encodes levels 0..4 from the tiles it holds (they never reach
+    // d_chain); the stand-alone encoder takes the remaining small levels
+    const int fused_levels = do_mips && do_blocks ? mips_fused_encode_levels(c, r.format) : 0;
     if (do_mips && c.levels > 1 || (do_mips && r.normal_map)) {
-        int n = launch_mips(c, r.normal_map, r.normalize, d_rgba, d_chain, d_scratch, stream);
+        int n = launch_mips(c, r.normal_map, r.normalize, d_rgba, d_chain, d_scratch, stream, fused_levels ? r.format : -1,
+                            fused_levels ? d_blocks : nullptr);
         if (n < 0) return cuda_fail(cudaGetLastError(), "mip kernels");
         g_launches += (uint64_t)n;
     }
@@ -330,8 +334,10 @@ int encode_on_stream(const Chain& c, const Resolved& r, const uint8_t* d_rgba, u
         int n;
         if (r.format == ROSY_TEX_FORMAT_BC7)
             n = launch_bc7(c, 0, c.levels, r.quality, level0, d_chain, d_blocks, stream);
+        else if (fused_levels >= c.levels)
+            n = 0;
         else
-            n = launch_bc45(c, 0, c.levels, r.format == ROSY_TEX_FORMAT_BC5, level0, d_chain, d_blocks, stream);
+            n = launch_bc45(c, fused_levels, c.levels - fused_levels, r.format == ROSY_TEX_FORMAT_BC5, level0, d_chain, d_blocks, stream);
         if (n < 0) return cuda_fail(cudaGetLastError(), "encoder kernel");
         g_launches += (uint64_t)n;
     }
@@ -428,6 +434,19 @@ size_t batch_desc_bytes(int count) {
 int encode_batch_on_stream(int count, const Resolved* rs, const MipBatchItem* mi, uint8_t* const* d_blocks, void* d_desc,
                            cudaStream_t s, bool do_mips, bool do_blocks) {
     if (!d_desc) return fail(ROSY_TEX_ERR_ARG, "null batch scratch");
+    std::vector<int> fused_levels((size_t)count, 0);
+    std::vector<MipBatchItem> mi_enc;
+    if (do_mips && do_blocks) {
+        mi_enc.assign(mi, mi + count);
+        for (int i = 0; i < count; i++) {
+            fused_levels[(size_t)i] = mips_fused_encode_levels(mi[i].chain, rs[i].format);
+            if (fused_levels[(size_t)i]) {
+                mi_enc[(size_t)i].enc_format = rs[i].format;
+                mi_enc[(size_t)i].d_blocks = d_blocks[i];
+            }
+        }
+        mi = mi_enc.data();
+    }
     if (do_mips) {
         const int n = launch_mips_batch(count, mi, d_desc, s);
         if (n < 0) return cuda_fail(cudaGetLastError(), "batched mip kernels");
@@ -450,6 +469,7 @@ int encode_batch_on_stream(int count, const Resolved* rs, const MipBatchItem* mi
                 Bc45BatchItem a;
                 a.chain = mi[i].chain;
                 a.bc5 = rs[i].format == ROSY_TEX_FORMAT_BC5;
+                a.first_level = fused_levels[(size_t)i];
                 a.d_level0 = level0;
                 a.d_chain = mi[i].d_chain;
                 a.d_blocks = d_blocks[i];

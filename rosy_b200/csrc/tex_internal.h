@@ -39,8 +39,11 @@ Bc7Tier bc7_tier(int quality);
 
 // ---- kernel launchers (each returns the number of kernels it launched, or -1 on error) ----
 // mip_kernels.cu
+// enc_format / d_blocks: ROSY_TEX_FORMAT_BC5 / _BC4 and the texture's block stream let the fused kernel encode levels
+// 0 .. mips_fused_encode_levels() - 1 itself (they are then NOT written to d_chain); -1 / nullptr: mips only
 int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba,
-                uint8_t* d_chain, void* d_scratch, cudaStream_t s);
+                uint8_t* d_chain, void* d_scratch, cudaStream_t s, int enc_format = -1, uint8_t* d_blocks = nullptr);
+int mips_fused_encode_levels(const Chain& c, int format);
 size_t mips_scratch_bytes(const Chain& c);
 // several textures, one fused launch per image kind (ragged extents fall back to per-level launches)
 struct MipBatchItem {
@@ -50,6 +53,8 @@ struct MipBatchItem {
     const uint8_t* d_rgba;
     uint8_t* d_chain;
     void* d_scratch;  // mips_scratch_bytes(chain), first 256 bytes zero
+    int enc_format = -1;          // see launch_mips
+    uint8_t* d_blocks = nullptr;
 };
 size_t mips_batch_desc_bytes(int n);
 int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream_t s);
@@ -59,6 +64,7 @@ int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const
 struct Bc45BatchItem {
     Chain chain;
     bool bc5;
+    int first_level;          // first level this launch encodes (levels below it came out of the fused mip kernel)
     const uint8_t* d_level0;  // level 0 pixels when they are not in the chain buffer (colour maps), else nullptr
     const uint8_t* d_chain;
     uint8_t* d_blocks;

@@ -407,6 +407,32 @@ def test_fused_mip_kernel_shapes(tex, oracle, synth, size):
         _chain_check(tex, oracle, synth.make(name, w, h, index), kind, normalize)
 
 
+@pytest.mark.parametrize("size", [(64, 64), (192, 320), (1024, 512), (2048, 2048)])
+def test_fused_mip_encode_equals_separate_stages(tex, oracle, synth, size):
+    """BC5 / BC4: levels 0..4 are encoded inside the fused mip kernel (one block per thread, per four lanes, and by the
+    auxiliary warp); the .dds must hold exactly the blocks the stand-alone encoder gives for the chain that
+    rosy_tex_mips_rgba8 returns (same mip arithmetic, stb_dxt block for block), for every image kind"""
+    w, h = size
+    cases = [("normal", 1, tex.KIND_NORMAL_MAP, tex.FORMAT_BC5, 1), ("normal", 4, tex.KIND_NORMAL_MAP, tex.FORMAT_BC5, 0),
+             ("normal", 2, tex.KIND_NORMAL_MAP, tex.FORMAT_BC4, 1), ("metal_rough", 2, tex.KIND_METALLIC_ROUGHNESS, tex.FORMAT_BC4, -1),
+             ("albedo", 7, tex.KIND_COLOR, tex.FORMAT_BC5, -1), ("random", 3, tex.KIND_COLOR, tex.FORMAT_BC4, -1)]
+    for name, index, kind, fmt, normalize in cases:
+        if w * h > 1024 * 1024 and name in ("random", "albedo"):
+            continue
+        img = synth.make(name, w, h, index)
+        got = tex.encode_rgba8(img, kind, fmt, 1, normalize=normalize)
+        levels = tex.mips_rgba8(img, kind, normalize=normalize)
+        off, bb = 148, (8 if fmt == tex.FORMAT_BC4 else 16)
+        for l, lv in enumerate(levels):
+            lh, lw = lv.shape[:2]
+            n = ((lw + 3) // 4) * ((lh + 3) // 4) * bb
+            want = oracle.encode_image(lv, fmt)
+            bad = np.nonzero((got[off : off + n].reshape(-1, bb) != want.reshape(-1, bb)).any(axis=1))[0]
+            assert bad.size == 0, f"{name} {w}x{h} fmt {fmt} level {l}: {bad.size} blocks differ, first {bad[:4]}"
+            off += n
+        assert off == got.size
+
+
 def test_mip_chain_fraction_of_exact_matches(tex, oracle, synth):
     """the <= 1 LSB bar is met with almost every texel identical to the oracle's"""
     for name, index, kind in [("albedo", 0, tex.KIND_COLOR), ("albedo", 7, tex.KIND_COLOR), ("normal", 1, tex.KIND_NORMAL_MAP)]:
