@@ -60,6 +60,8 @@ def parse_args():
     ap.add_argument("--files", type=int, default=16, help="image files in the e2e_files leg (0: skip)")
     ap.add_argument("--per-texture", action="store_true",
                     help="device leg: one mip launch per texture (rosy_tex_mips_device) instead of the batched call")
+    ap.add_argument("--split-stages", action="store_true",
+                    help="BC5 / BC4: mips and blocks as two calls (two kernels timed apart) instead of the fused mip + encode kernel")
     return ap.parse_args()
 
 
@@ -316,6 +318,8 @@ def main():
         flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
 
+    fused = fmt != T.FORMAT_BC7 and not args.split_stages and not args.per_texture and os.environ.get("ROSY_TEX_FUSE_ENCODE", "1") != "0"
+
     def step(events=None):
         if flush is not None:
             flush.fill_(1)
@@ -334,6 +338,14 @@ def main():
         if events is not None:
             ea, eb, ec = events[0]
             ea.record()
+        if fused:
+            # BC5 / BC4: ONE call for both stages, so that the fused mip + encode kernel runs (levels 0..4 are encoded
+            # from the tiles the mip kernel holds; a small bc45_encode_kernel launch takes levels 5..)
+            T.encode_batch_device(batch, d_batch.data_ptr(), stream, True, True)
+            if events is not None:
+                eb.record()
+                ec.record()
+            return
         T.encode_batch_device(batch, d_batch.data_ptr(), stream, True, False)
         if events is not None:
             eb.record()
@@ -440,8 +452,11 @@ def main():
     chain_px = chain_bytes // 4
     mip_bytes = (4 * npx + 4 * (chain_px - npx) + (4 * npx if kind == T.KIND_NORMAL_MAP else 0)) * mip_tex_per_launch
     enc_bytes = (4 * chain_px + blk_bytes) * enc_tex_per_launch
+    if fused:
+        # SURVEY 8(d) fused floor: level 0 read once, every level's blocks written once
+        mip_bytes = (4 * npx + blk_bytes) * mip_tex_per_launch
     mip_gbs = mip_bytes / (mip_ms * 1e-3) / 1e9
-    enc_gbs = enc_bytes / (enc_ms * 1e-3) / 1e9
+    enc_gbs = enc_bytes / (enc_ms * 1e-3) / 1e9 if enc_ms > 0 else 0.0
     prof = load_profile_counts(args)
     sm_mhz = clk["sm_mhz"] or float(peaks.get("sm_max_mhz", 1965.0))
     issue_peak = SM_COUNT * 4 * sm_mhz * 1e6 / 1e9  # G warp-instructions / s at the clock seen under load
@@ -468,6 +483,15 @@ def main():
             roofline["achieved"] = a
             roofline["frac"] = a / issue_peak
             roofline["inst_source"] = prof.get("source")
+    elif fused:
+        roofline = {
+            "kernel": "mip_fused_kernel<ENC> (mip chain + BC5/BC4 blocks of levels 0..4) + bc45_encode_kernel (levels 5..)",
+            "bound": "hbm", "achieved": mip_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": mip_gbs / hbm_peak, "traffic": None,
+            "ms_per_launch": mip_ms, "share_of_step": mip_ms / ms_step, "algorithmic_bytes_per_launch": mip_bytes,
+            "textures_per_launch": mip_tex_per_launch, "peak_source": peak_src,
+            "note": "algorithmic bytes = SURVEY 8(d)'s fused floor: 4 N read + the block stream written; the separate stages "
+            "(--split-stages) move 4 N + 4 N/3 (+ 4 N for normal maps) and then 4 (4 N/3) + blocks",
+        }
     else:
         roofline = {
             "kernel": enc_kernel, "bound": "hbm", "achieved": enc_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -475,7 +499,7 @@ def main():
             "share_of_step": enc_ms * (n // enc_tex_per_launch) / ms_step, "algorithmic_bytes_per_launch": enc_bytes,
             "peak_source": peak_src,
         }
-    roofline_mip = {
+    roofline_mip = None if fused else {
         "kernel": "mip_fused_kernel", "bound": "hbm", "achieved": mip_gbs, "peak": hbm_peak, "unit": "GB/s",
         "frac": mip_gbs / hbm_peak, "traffic": (prof["mip_dram_bytes_per_texture"] * mip_tex_per_launch if prof.get("mip_dram_bytes_per_texture") else None),
         "ms_per_launch": mip_ms,

@@ -102,6 +102,33 @@ __device__ __forceinline__ uint2 alpha_block(const uint32_t v[4], const uint32_t
     return make_uint2((uint32_t)mx | ((uint32_t)mn << 8) | (lo << 16), (lo >> 16) | (hi << 8));
 }
 
+// The same block from sixteen samples given as BASE + v (v = the 8-bit value; BASE = e.g. the exponent bits of a
+// float whose low mantissa byte holds v): min / max compare the raw words, and BASE * M7 is folded into the additive
+// constant of the quotient's multiply-add (arithmetic modulo 2^32), so the samples are never unpacked.
+template <uint32_t BASE>
+__device__ __forceinline__ uint2 alpha_block_raw(const uint32_t s[16], const uint32_t* recip) {
+    int mn = (int)s[0], mx = (int)s[0];
+#pragma unroll
+    for (int i = 1; i < 15; i += 2) {
+        mn = __vimin3_s32(mn, (int)s[i], (int)s[i + 1]);
+        mx = __vimax3_s32(mx, (int)s[i], (int)s[i + 1]);
+    }
+    mn = min(mn, (int)s[15]) - (int)BASE;
+    mx = max(mx, (int)s[15]) - (int)BASE;
+    uint32_t M7, biasM;
+    quotient_consts(mn, mx, recip, M7, biasM);
+    biasM -= BASE * M7;
+    uint32_t nib[2] = {0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const uint32_t t = mad_u32(s[i], M7, biasM);
+        const int j = i & 7, sh = 20 - 4 * j;
+        nib[i >> 3] |= (sh >= 0 ? t >> sh : t << -sh) & (7u << (4 * j));
+    }
+    const uint32_t lo = map_and_pack8(nib[0]), hi = map_and_pack8(nib[1]);
+    return make_uint2((uint32_t)mx | ((uint32_t)mn << 8) | (lo << 16), (lo >> 16) | (hi << 8));
+}
+
 // sixteen RGBA8 texels of a block, row major -> byte-planar R (and G): texel 4k+j in byte j of word k
 __device__ __forceinline__ void planes_rg(const uint32_t px[16], uint32_t r4[4], uint32_t g4[4]) {
 #pragma unroll
@@ -114,25 +141,40 @@ __device__ __forceinline__ void planes_rg(const uint32_t px[16], uint32_t r4[4],
 }
 
 // One 4x4 block held by FOUR lanes {l, l^1, l^16, l^17} of a warp, a 2x2 quad of texels each (lane bit 0: right
-// half, lane bit 4: lower half; s[0..3] = the lane's samples of one channel in the order (0,0) (0,1) (1,0) (1,1)).
-// Every lane computes the indices of its own samples; the block's min / max and the 48 index bits are combined
-// with redux.sync over the four lanes.  Returns the two 32-bit words of the 8-byte block on every lane.
-__device__ __forceinline__ uint2 alpha_block_quad(const int s[4], const uint32_t* recip, uint32_t qmask, int dx, int dy) {
-    const int mn = (int)__reduce_min_sync(qmask, (unsigned)__vimin3_s32(s[0], s[1], min(s[2], s[3])));
-    const int mx = (int)__reduce_max_sync(qmask, (unsigned)__vimax3_s32(s[0], s[1], max(s[2], s[3])));
+// half, lane bit 4: lower half).  rg[0..3] = the lane's texels in the order (0,0) (0,1) (1,0) (1,1) as R | G << 16.
+// Every lane computes the indices of its own samples; the block's min / max (both channels at once, 16x2 SIMD
+// min / max) and the 48 index bits travel by xor shuffles (redux.sync would serialise the eight quads of a
+// warp: its result is warp-uniform).  Returns the two words of the 8-byte block of channel C on every lane.
+struct QuadMinMax {
+    uint32_t mn, mx;  // R | G << 16
+};
+__device__ __forceinline__ QuadMinMax quad_minmax(const uint32_t rg[4]) {
+    uint32_t mn = __vimin3_s16x2(__vimin3_s16x2(rg[0], rg[1], rg[2]), rg[3], rg[3]);
+    uint32_t mx = __vimax3_s16x2(__vimax3_s16x2(rg[0], rg[1], rg[2]), rg[3], rg[3]);
+    mn = __vimin3_s16x2(mn, mn, __shfl_xor_sync(0xFFFFFFFFu, mn, 1));
+    mx = __vimax3_s16x2(mx, mx, __shfl_xor_sync(0xFFFFFFFFu, mx, 1));
+    mn = __vimin3_s16x2(mn, mn, __shfl_xor_sync(0xFFFFFFFFu, mn, 16));
+    mx = __vimax3_s16x2(mx, mx, __shfl_xor_sync(0xFFFFFFFFu, mx, 16));
+    return {mn, mx};
+}
+template <int C>
+__device__ __forceinline__ uint2 alpha_block_quad(const uint32_t rg[4], QuadMinMax mm, const uint32_t* recip, int dx, int dy) {
+    const int mn = (int)((mm.mn >> (16 * C)) & 0xFFFFu), mx = (int)((mm.mx >> (16 * C)) & 0xFFFFu);
     uint32_t M7, biasM;
     quotient_consts(mn, mx, recip, M7, biasM);
     uint32_t nib = 0u;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        const uint32_t t = mad_u32((uint32_t)s[i], M7, biasM);
+        const uint32_t t = mad_u32((rg[i] >> (16 * C)) & 0xFFFFu, M7, biasM);
         const int sh = 20 - 4 * i;
         nib |= (t >> sh) & (7u << (4 * i));
     }
     const uint32_t r = map_index_nibbles(nib) & 0x7777u;
     const uint32_t pairs = (r & 0x0707u) | ((r >> 1) & 0x3838u);            // row 0 of the quad in bits 0..5, row 1 in bits 8..13
     const uint32_t V = ((pairs & 0x3Fu) | ((pairs & 0x3F00u) << 4)) << (6 * dx);  // texel (y, x) of a block half sits at bit 3 (4 y + x)
-    const uint32_t lo = __reduce_or_sync(qmask, dy ? 0u : V), hi = __reduce_or_sync(qmask, dy ? V : 0u);
+    const uint32_t W = V | __shfl_xor_sync(0xFFFFFFFFu, V, 1);   // this half of the block (rows 2 dy, 2 dy + 1), 24 bits
+    const uint32_t O = __shfl_xor_sync(0xFFFFFFFFu, W, 16);      // the other half
+    const uint32_t lo = dy ? O : W, hi = dy ? W : O;
     return make_uint2((uint32_t)mx | ((uint32_t)mn << 8) | (lo << 16), (lo >> 16) | (hi << 8));
 }
 

@@ -357,6 +357,15 @@ __device__ __forceinline__ uint32_t finish_opaque(float r_, float g_, float b_, 
     const uint32_t rg = __byte_perm(r, g, 0x0051);
     return __byte_perm(rg, b | 0x00FF0000u, 0x6510);  // r, g, b.b1, 0xFF
 }
+// fused encode: byte 1 of an srgb8_bits result as a raw sample (RAW_BASE + v, see normalize_texel_raw)
+__device__ __forceinline__ uint32_t raw_of_srgb8(uint32_t bits) { return __byte_perm(bits, 0x4B000000u, 0x7441); }
+// finish_colour restricted to R (and G)
+template <int NCH>
+__device__ __forceinline__ void finish_colour_raw(float4 v, const float2* tab, uint32_t& r, uint32_t& g) {
+    const float ia = v.w > 1e-12f ? rcp_approx(v.w) : 1.0f;
+    r = raw_of_srgb8(srgb8_bits(fminf(fmaxf(v.x * ia, SRGB_BIAS), SRGB_MAX), tab));
+    if (NCH > 1) g = raw_of_srgb8(srgb8_bits(fminf(fmaxf(v.y * ia, SRGB_BIAS), SRGB_MAX), tab));
+}
 // packed fp32 pair add (FADD2)
 __device__ __forceinline__ float2 add2(float2 a, float2 b) {
     unsigned long long ra, rb, rd;
@@ -368,6 +377,13 @@ __device__ __forceinline__ float2 add2(float2 a, float2 b) {
     return d;
 }
 
+// MUFU.RSQ alone: rsqrtf() adds a rescaling path for denormal arguments, which never occur here (identical results)
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // ---- normal maps ---------------------------------------------------------------------------
 // Surface::normalizeNormalMap on one 8-bit texel (level 0): d = 2 v - 255 exactly, n = d / |d|,
 // out = floor(127.5 n + 128) = floor(255 (n/2 + 1/2) + 0.5); alpha passes through.
@@ -377,7 +393,7 @@ __device__ __forceinline__ uint32_t normalize_texel(uint32_t p) {
     const float dy = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7514)) - 8421376.0f;
     const float dz = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7524)) - 8421376.0f;
     const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));  // d is odd in every channel: never zero
-    const float s = rsqrtf(l2) * 127.5f;
+    const float s = rsqrt_approx(l2) * 127.5f;
     const uint32_t r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
     const uint32_t g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
     const uint32_t b = __float_as_uint(__fmaf_rd(dz, s, 8388736.0f));
@@ -400,13 +416,49 @@ __device__ __forceinline__ uint32_t finish_normal_sums(uint32_t rb, uint32_t ga,
     const float dz = __uint_as_float(__byte_perm(rb, 0x4B000000u, 0x7432)) - k2;
     const float dy = __uint_as_float(__byte_perm(ga, 0x4B000000u, 0x7410)) - k2;
     const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-    const float s = l2 > 0.0f ? rsqrtf(l2) * 127.5f : 0.0f;
+    const float s = l2 > 0.0f ? rsqrt_approx(l2) * 127.5f : 0.0f;
     const uint32_t r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
     const uint32_t g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
     const uint32_t b = __float_as_uint(__fmaf_rd(dz, s, 8388736.0f));
     const uint32_t a = ((ga >> 16) + half) >> (2 * K);
     const uint32_t rg = __byte_perm(r, g, 0x0040);
     return __byte_perm(rg, __byte_perm(b, a, 0x0040), 0x5410);
+}
+
+// ---- fused encode: R (and G) only, as RAW samples = RAW_BASE + v (the float 2^23 + v), which is what the round-down
+// multiply-add of the normalisation leaves in a register; bc45::alpha_block_raw consumes them as they are ----
+constexpr uint32_t RAW_BASE = 0x4B000000u;
+template <int NCH>
+__device__ __forceinline__ void normalize_texel_raw(uint32_t p, int normalize, uint32_t& r, uint32_t& g) {
+    if (normalize) {
+        const float dx = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7504)) - 8421376.0f;
+        const float dy = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7514)) - 8421376.0f;
+        const float dz = __uint_as_float(__byte_perm(p, 0x4B000080u, 0x7524)) - 8421376.0f;
+        const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+        const float s = rsqrt_approx(l2) * 127.5f;
+        r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
+        if (NCH > 1) g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
+    } else {
+        r = __byte_perm(p, RAW_BASE, 0x7440);
+        if (NCH > 1) g = __byte_perm(p, RAW_BASE, 0x7441);
+    }
+}
+template <int K, int NCH>
+__device__ __forceinline__ void finish_normal_sums_raw(uint32_t rb, uint32_t ga, int normalize, uint32_t& r, uint32_t& g) {
+    constexpr uint32_t half = 1u << (2 * K - 1);
+    if (!normalize) {
+        r = (((rb + half) >> (2 * K)) & 0xFFu) | RAW_BASE;
+        if (NCH > 1) g = (((ga + half) >> (2 * K)) & 0xFFu) | RAW_BASE;
+        return;
+    }
+    constexpr float k2 = 8388608.0f + 255.0f * (float)(1 << (2 * K - 1));
+    const float dx = __uint_as_float(__byte_perm(rb, 0x4B000000u, 0x7410)) - k2;
+    const float dz = __uint_as_float(__byte_perm(rb, 0x4B000000u, 0x7432)) - k2;
+    const float dy = __uint_as_float(__byte_perm(ga, 0x4B000000u, 0x7410)) - k2;
+    const float l2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+    const float s = l2 > 0.0f ? rsqrt_approx(l2) * 127.5f : 0.0f;
+    r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
+    if (NCH > 1) g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
 }
 
 template <bool NORMAL>
@@ -527,32 +579,19 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 
 // ---- fused encode helpers (ENC 1: BC5 from bytes 0 and 1 of the RGBA8 texels, ENC 2: BC4 from byte 0) ----
-// one thread holds the whole block (row major)
+// four lanes {l, l^1, l^16, l^17} hold one block, a 2x2 quad each; every lane stores one 32-bit word of it.
+// r / g: the lane's raw samples (RAW_BASE + v), order (0,0) (0,1) (1,0) (1,1)
 template <int ENC>
-__device__ __forceinline__ void encode_own_block(const uint32_t px[16], const uint32_t* recip, uint8_t* blocks, uint32_t bi) {
-    uint32_t r4[4], g4[4];
-    bc45::planes_rg(px, r4, g4);
-    const uint2 rblk = bc45::alpha_block(r4, recip);
-    if (ENC == 1) {
-        const uint2 gblk = bc45::alpha_block(g4, recip);
-        *reinterpret_cast<uint4*>(blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
-    } else {
-        *reinterpret_cast<uint2*>(blocks + (size_t)bi * 8) = rblk;
-    }
-}
-// four lanes hold the block, a 2x2 quad each (w[row][col]); every lane stores one 32-bit word of it
-template <int ENC>
-__device__ __forceinline__ void encode_quad_block(const uint32_t w[2][2], const uint32_t* recip, uint32_t qmask, int dx, int dy,
-                                                  uint8_t* blocks, uint32_t bi) {
+__device__ __forceinline__ void encode_quad_block_raw(const uint32_t r[4], const uint32_t g[4], const uint32_t* recip, int dx, int dy,
+                                                      uint8_t* blocks, uint32_t bi) {
     const int q = dx | (dy << 1);
-    int s[4];
+    uint32_t rg[4];
 #pragma unroll
-    for (int i = 0; i < 4; i++) s[i] = (int)(w[i >> 1][i & 1] & 255u);
-    const uint2 rblk = bc45::alpha_block_quad(s, recip, qmask, dx, dy);
+    for (int i = 0; i < 4; i++) rg[i] = ENC == 1 ? __byte_perm(r[i], g[i], 0x5410) : (r[i] & 0xFFFFu);  // R | G << 16
+    const bc45::QuadMinMax mm = bc45::quad_minmax(rg);
+    const uint2 rblk = bc45::alpha_block_quad<0>(rg, mm, recip, dx, dy);
     if (ENC == 1) {
-#pragma unroll
-        for (int i = 0; i < 4; i++) s[i] = (int)((w[i >> 1][i & 1] >> 8) & 255u);
-        const uint2 gblk = bc45::alpha_block_quad(s, recip, qmask, dx, dy);
+        const uint2 gblk = bc45::alpha_block_quad<1>(rg, mm, recip, dx, dy);
         const uint32_t word = q == 0 ? rblk.x : (q == 1 ? rblk.y : (q == 2 ? gblk.x : gblk.y));
         reinterpret_cast<uint32_t*>(blocks + (size_t)bi * 16)[q] = word;
     } else if (dy == 0) {
@@ -763,9 +802,19 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 v6 = scale4(bfly(add4(v5a, v5b), 4), 0.25f);
                 const float4 s4 = useB ? v4b : v4a, s5 = useB ? v5b : v5a;
                 const float4 vc = role == 4 ? s4 : (role == 5 ? s5 : v6);
-                px3a = finish_colour(va, tab);
-                px3b = finish_colour(vb, tab);
-                pxc = finish_colour(vc, tab);
+                if (ENC) {  // R | G << 8 is all the block encoder wants of levels 3 and 4; levels 5, 6 go to the chain
+                    constexpr int NCH = ENC == 1 ? 2 : 1;
+                    uint32_t r_, g_ = 0u;
+                    finish_colour_raw<NCH>(va, tab, r_, g_);
+                    px3a = __byte_perm(r_, g_, 0x0040);
+                    finish_colour_raw<NCH>(vb, tab, r_, g_);
+                    px3b = __byte_perm(r_, g_, 0x0040);
+                    pxc = finish_colour(vc, tab);  // one pass for every role; the level-4 lanes use its low 16 bits
+                } else {
+                    px3a = finish_colour(va, tab);
+                    px3b = finish_colour(vb, tab);
+                    pxc = finish_colour(vc, tab);
+                }
             } else {
                 const uint2* qa = reinterpret_cast<const uint2*>(l2ring + b * 256) + (2 * Ya) * 16 + 2 * X;
                 const uint2* qb = qa + 8 * 16;
@@ -788,9 +837,21 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 const float4 v5a = scale4(bfly(bfly(v4a, 2), 16), 0.25f);
                 const float4 v5b = scale4(bfly(bfly(v4b, 2), 16), 0.25f);
                 v6 = scale4(bfly(add4(v5a, v5b), 4), 0.25f);
-                px3a = finish_normal_sums<3>(rb3a, ga3a, I.normalize);
-                px3b = finish_normal_sums<3>(rb3b, ga3b, I.normalize);
-                const uint32_t p4 = finish_normal_sums<4>(useB ? rb4b : rb4a, useB ? ga4b : ga4a, I.normalize);
+                uint32_t p4;
+                if (ENC) {  // R | G << 8 is all the block encoder wants of levels 3 and 4
+                    constexpr int NCH = ENC == 1 ? 2 : 1;
+                    uint32_t r_, g_ = 0u;
+                    finish_normal_sums_raw<3, NCH>(rb3a, ga3a, I.normalize, r_, g_);
+                    px3a = __byte_perm(r_, g_, 0x0040);
+                    finish_normal_sums_raw<3, NCH>(rb3b, ga3b, I.normalize, r_, g_);
+                    px3b = __byte_perm(r_, g_, 0x0040);
+                    finish_normal_sums_raw<4, NCH>(useB ? rb4b : rb4a, useB ? ga4b : ga4a, I.normalize, r_, g_);
+                    p4 = __byte_perm(r_, g_, 0x0040);
+                } else {
+                    px3a = finish_normal_sums<3>(rb3a, ga3a, I.normalize);
+                    px3b = finish_normal_sums<3>(rb3b, ga3b, I.normalize);
+                    p4 = finish_normal_sums<4>(useB ? rb4b : rb4a, useB ? ga4b : ga4a, I.normalize);
+                }
                 const float4 s5 = useB ? v5b : v5a;
                 const uint32_t pf = finish_pixel<true>(role == 5 ? s5 : v6, I.normalize);
                 pxc = role == 4 ? p4 : pf;
@@ -912,34 +973,46 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         if (lane == 0) mbar_arrive(&S.empty[s]);  // the texels are in registers: the stage may be refilled
         const int b = it % L3_BUFS;
         // fused encode: the level-1 texels of this thread (2x2) and its level-2 texel, as the chain would hold them
-        uint32_t l1w[2][2], px2 = 0u;
-        const uint32_t qmask = 0x00030003u << (lane & 0x0E);  // the four lanes that share a level-1 block
+        uint32_t px2 = 0u;
         const int qdx = lane & 1, qdy = (lane >> 4) & 1;
 
         if (NORMAL) {
             // level 0 of a normal map is the re-normalised input (Packager.cpp:294-296 at mip 0)
-            uint32_t blk0[16];
+            if (ENC) {
+                // R (and G) of the sixteen re-normalised texels as raw samples, straight into the block encoder
+                constexpr int NCH = ENC == 1 ? 2 : 1;
+                uint32_t sr[16], sg[16];
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                uint4 o = rows[r];
-                if (normalize) {
-                    o.x = normalize_texel(o.x);
-                    o.y = normalize_texel(o.y);
-                    o.z = normalize_texel(o.z);
-                    o.w = normalize_texel(o.w);
+                for (int r = 0; r < 4; r++) {
+                    normalize_texel_raw<NCH>(rows[r].x, normalize, sr[4 * r + 0], sg[4 * r + 0]);
+                    normalize_texel_raw<NCH>(rows[r].y, normalize, sr[4 * r + 1], sg[4 * r + 1]);
+                    normalize_texel_raw<NCH>(rows[r].z, normalize, sr[4 * r + 2], sg[4 * r + 2]);
+                    normalize_texel_raw<NCH>(rows[r].w, normalize, sr[4 * r + 3], sg[4 * r + 3]);
                 }
-                if (ENC) {
-                    blk0[4 * r + 0] = o.x;
-                    blk0[4 * r + 1] = o.y;
-                    blk0[4 * r + 2] = o.z;
-                    blk0[4 * r + 3] = o.w;
+                const uint32_t bi = I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx;
+                const uint2 rblk = bc45::alpha_block_raw<RAW_BASE>(sr, E.recip);
+                if (ENC == 1) {
+                    const uint2 gblk = bc45::alpha_block_raw<RAW_BASE>(sg, E.recip);
+                    *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
                 } else {
+                    *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    uint4 o = rows[r];
+                    if (normalize) {
+                        o.x = normalize_texel(o.x);
+                        o.y = normalize_texel(o.y);
+                        o.z = normalize_texel(o.z);
+                        o.w = normalize_texel(o.w);
+                    }
                     c0[(size_t)r * (w0 / 4)] = o;
                 }
             }
-            if (ENC) encode_own_block<ENC>(blk0, E.recip, I.blocks, I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx);
             // exact integer channel sums, two 16-bit lanes per word
             uint32_t rb2 = 0, ga2 = 0;
+            uint32_t l1r[4], l1g[4];  // fused encode: this thread's 2x2 level-1 texels as raw samples
 #pragma unroll
             for (int j = 0; j < 2; j++) {
                 const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
@@ -949,92 +1022,155 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 const uint32_t rb_r = (a.z & 0x00FF00FFu) + (a.w & 0x00FF00FFu) + (bq.z & 0x00FF00FFu) + (bq.w & 0x00FF00FFu);
                 const uint32_t ga_r = ((a.z >> 8) & 0x00FF00FFu) + ((a.w >> 8) & 0x00FF00FFu) +
                                       ((bq.z >> 8) & 0x00FF00FFu) + ((bq.w >> 8) & 0x00FF00FFu);
-                const uint2 o1 = make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
                 if (ENC) {
-                    l1w[j][0] = o1.x;
-                    l1w[j][1] = o1.y;
+                    finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_l, ga_l, normalize, l1r[2 * j], l1g[2 * j]);
+                    finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_r, ga_r, normalize, l1r[2 * j + 1], l1g[2 * j + 1]);
                 } else {
-                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = o1;
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
+                        make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
                 }
                 rb2 += rb_l + rb_r;
                 ga2 += ga_l + ga_r;
             }
-            px2 = finish_normal_sums<2>(rb2, ga2, normalize);
-            if (!ENC) *c2 = px2;
+            if (ENC) {
+                uint32_t r2, g2 = 0u;
+                finish_normal_sums_raw<2, ENC == 1 ? 2 : 1>(rb2, ga2, normalize, r2, g2);
+                px2 = __byte_perm(r2, g2, 0x0040);  // R | G << 8
+                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
+            } else {
+                *c2 = finish_normal_sums<2>(rb2, ga2, normalize);
+            }
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
             reinterpret_cast<uint2*>(l2ring + b * 256)[tid] = make_uint2(rb2, ga2);
         } else {
-            if (ENC) {  // colour maps: level 0 is the input itself (Packager.cpp:245 at mip 0)
-                const uint32_t blk0[16] = {rows[0].x, rows[0].y, rows[0].z, rows[0].w, rows[1].x, rows[1].y, rows[1].z, rows[1].w,
-                                           rows[2].x, rows[2].y, rows[2].z, rows[2].w, rows[3].x, rows[3].y, rows[3].z, rows[3].w};
-                encode_own_block<ENC>(blk0, E.recip, I.blocks, I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx);
-            }
             uint32_t all = rows[0].x & rows[0].y & rows[0].z & rows[0].w;
 #pragma unroll
             for (int r = 1; r < 4; r++) all &= rows[r].x & rows[r].y & rows[r].z & rows[r].w;
             const bool opaque = __all_sync(0xFFFFFFFFu, all >= 0xFF000000u);
             float4 v2;
-            if (opaque) {
-                float2 srg = make_float2(0.f, 0.f);
-                float sb = 0.f;
+            if (ENC) {
+                // Fused encode of a colour map: only R (BC4) or R and G (BC5) are ever looked at, so only they are
+                // computed - same arithmetic per channel as below - and handed to the encoders as raw samples.
+                constexpr int NCH = ENC == 1 ? 2 : 1;
+                {   // level 0 is the input itself (Packager.cpp:245 at mip 0)
+                    uint32_t sr[16], sg[16];
 #pragma unroll
-                for (int j = 0; j < 2; j++) {
-                    const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
-                    uint32_t o[2];
-#pragma unroll
-                    for (int i = 0; i < 2; i++) {
-                        const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
-                        const float2 rg = add2(add2(make_float2(lin_lookup<0>(lanebase, p0), lin_lookup<1>(lanebase, p0)),
-                                                    make_float2(lin_lookup<0>(lanebase, p1), lin_lookup<1>(lanebase, p1))),
-                                               add2(make_float2(lin_lookup<0>(lanebase, p2), lin_lookup<1>(lanebase, p2)),
-                                                    make_float2(lin_lookup<0>(lanebase, p3), lin_lookup<1>(lanebase, p3))));
-                        const float b_ = (lin_lookup<2>(lanebase, p0) + lin_lookup<2>(lanebase, p1)) + (lin_lookup<2>(lanebase, p2) + lin_lookup<2>(lanebase, p3));
-                        o[i] = finish_opaque(rg.x, rg.y, b_, tab);
-                        srg = add2(srg, rg);
-                        sb += b_;
-                    }
-                    if (ENC) {
-                        l1w[j][0] = o[0];
-                        l1w[j][1] = o[1];
-                    } else {
-                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
-                    }
-                }
-                v2 = make_float4(srg.x * 0.25f, srg.y * 0.25f, sb * 0.25f, 1.0f);
-                px2 = finish_opaque(v2.x, v2.y, v2.z, tab);
-                if (!ENC) *c2 = px2;
-            } else {
-                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int j = 0; j < 2; j++) {
-                    const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
-                    uint32_t o[2];
-#pragma unroll
-                    for (int i = 0; i < 2; i++) {
-                        const uint32_t p[4] = {i ? a.z : a.x, i ? a.w : a.y, i ? bq.z : bq.x, i ? bq.w : bq.y};
-                        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int r = 0; r < 4; r++) {
+                        const uint32_t p[4] = {rows[r].x, rows[r].y, rows[r].z, rows[r].w};
 #pragma unroll
                         for (int k = 0; k < 4; k++) {
-                            const float al = alpha_lookup(lanebase, p[k]);
-                            q.x = fmaf(lin_lookup<0>(lanebase, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
-                            q.y = fmaf(lin_lookup<1>(lanebase, p[k]), al, q.y);
-                            q.z = fmaf(lin_lookup<2>(lanebase, p[k]), al, q.z);
-                            q.w += al;
+                            sr[4 * r + k] = __byte_perm(p[k], RAW_BASE, 0x7440);
+                            if (NCH > 1) sg[4 * r + k] = __byte_perm(p[k], RAW_BASE, 0x7441);
                         }
-                        q.w *= 0.25f;
-                        o[i] = finish_colour(q, tab);
-                        sum = add4(sum, q);
                     }
-                    if (ENC) {
-                        l1w[j][0] = o[0];
-                        l1w[j][1] = o[1];
+                    const uint32_t bi = I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx;
+                    const uint2 rblk = bc45::alpha_block_raw<RAW_BASE>(sr, E.recip);
+                    if (ENC == 1) {
+                        const uint2 gblk = bc45::alpha_block_raw<RAW_BASE>(sg, E.recip);
+                        *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
                     } else {
-                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                        *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
                     }
                 }
-                v2 = scale4(sum, 0.25f);
-                px2 = finish_colour(v2, tab);
-                if (!ENC) *c2 = px2;
+                uint32_t l1r[4], l1g[4], r2, g2 = 0u;
+                if (opaque) {
+                    float sr_ = 0.f, sg_ = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+#pragma unroll
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
+                            const float r_ = (lin_lookup<0>(lanebase, p0) + lin_lookup<0>(lanebase, p1)) + (lin_lookup<0>(lanebase, p2) + lin_lookup<0>(lanebase, p3));
+                            l1r[2 * j + i] = raw_of_srgb8(srgb8_bits(r_, tab));
+                            sr_ += r_;
+                            if (NCH > 1) {
+                                const float g_ = (lin_lookup<1>(lanebase, p0) + lin_lookup<1>(lanebase, p1)) + (lin_lookup<1>(lanebase, p2) + lin_lookup<1>(lanebase, p3));
+                                l1g[2 * j + i] = raw_of_srgb8(srgb8_bits(g_, tab));
+                                sg_ += g_;
+                            }
+                        }
+                    }
+                    v2 = make_float4(sr_ * 0.25f, sg_ * 0.25f, 0.0f, 1.0f);
+                    r2 = raw_of_srgb8(srgb8_bits(v2.x, tab));
+                    if (NCH > 1) g2 = raw_of_srgb8(srgb8_bits(v2.y, tab));
+                } else {
+                    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+#pragma unroll
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t p[4] = {i ? a.z : a.x, i ? a.w : a.y, i ? bq.z : bq.x, i ? bq.w : bq.y};
+                            float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                const float al = alpha_lookup(lanebase, p[k]);
+                                q.x = fmaf(lin_lookup<0>(lanebase, p[k]), al, q.x);
+                                if (NCH > 1) q.y = fmaf(lin_lookup<1>(lanebase, p[k]), al, q.y);
+                                q.w += al;
+                            }
+                            q.w *= 0.25f;
+                            finish_colour_raw<NCH>(q, tab, l1r[2 * j + i], l1g[2 * j + i]);
+                            sum = add4(sum, q);
+                        }
+                    }
+                    v2 = scale4(sum, 0.25f);
+                    finish_colour_raw<NCH>(v2, tab, r2, g2);
+                }
+                px2 = __byte_perm(r2, g2, 0x0040);  // R | G << 8
+                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
+            } else {
+                if (opaque) {
+                    float2 srg = make_float2(0.f, 0.f);
+                    float sb = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+                        uint32_t o[2];
+#pragma unroll
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t p0 = i ? a.z : a.x, p1 = i ? a.w : a.y, p2 = i ? bq.z : bq.x, p3 = i ? bq.w : bq.y;
+                            const float2 rg = add2(add2(make_float2(lin_lookup<0>(lanebase, p0), lin_lookup<1>(lanebase, p0)),
+                                                        make_float2(lin_lookup<0>(lanebase, p1), lin_lookup<1>(lanebase, p1))),
+                                                   add2(make_float2(lin_lookup<0>(lanebase, p2), lin_lookup<1>(lanebase, p2)),
+                                                        make_float2(lin_lookup<0>(lanebase, p3), lin_lookup<1>(lanebase, p3))));
+                            const float b_ = (lin_lookup<2>(lanebase, p0) + lin_lookup<2>(lanebase, p1)) + (lin_lookup<2>(lanebase, p2) + lin_lookup<2>(lanebase, p3));
+                            o[i] = finish_opaque(rg.x, rg.y, b_, tab);
+                            srg = add2(srg, rg);
+                            sb += b_;
+                        }
+                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    }
+                    v2 = make_float4(srg.x * 0.25f, srg.y * 0.25f, sb * 0.25f, 1.0f);
+                    *c2 = finish_opaque(v2.x, v2.y, v2.z, tab);
+                } else {
+                    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const uint4 a = rows[2 * j], bq = rows[2 * j + 1];
+                        uint32_t o[2];
+#pragma unroll
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t p[4] = {i ? a.z : a.x, i ? a.w : a.y, i ? bq.z : bq.x, i ? bq.w : bq.y};
+                            float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                const float al = alpha_lookup(lanebase, p[k]);
+                                q.x = fmaf(lin_lookup<0>(lanebase, p[k]), al, q.x);  // premultiplyAlpha; table holds linear / 4
+                                q.y = fmaf(lin_lookup<1>(lanebase, p[k]), al, q.y);
+                                q.z = fmaf(lin_lookup<2>(lanebase, p[k]), al, q.z);
+                                q.w += al;
+                            }
+                            q.w *= 0.25f;
+                            o[i] = finish_colour(q, tab);
+                            sum = add4(sum, q);
+                        }
+                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                    }
+                    v2 = scale4(sum, 0.25f);
+                    *c2 = finish_colour(v2, tab);
+                }
             }
             // levels 3.. are the auxiliary warp's: hand over this thread's level-2 value
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
@@ -1043,8 +1179,6 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         if (ENC) {
             // the l3empty wait above also covers the level-2 texel buffer
             E.l2rg[grp][b][tid] = (uint16_t)px2;
-            // level 1: one block per four lanes
-            encode_quad_block<ENC>(l1w, E.recip, qmask, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.l3full[b]);

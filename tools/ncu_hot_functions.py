@@ -1,11 +1,15 @@
 """Join an `ncu --page source --csv` dump (per-SASS-instruction counters) with nvdisasm -g line info
 and aggregate by source function: executed instructions, stall samples, no-instruction stalls.
     ncu -i rep.ncu-rep --page source --csv > src.csv
-    python tools/ncu_hot_functions.py src.csv rosy_b200/csrc/bc7_encode.o rosy_b200/csrc/bc7_encode.cu
+    python tools/ncu_hot_functions.py src.csv rosy_b200/csrc/bc7_encode.o rosy_b200/csrc/bc7_encode.cu [section-substring] [--lines N]
+An object with several kernels has one .text section per kernel and instruction offsets restart in each: pass a substring of
+the mangled name of the profiled kernel (e.g. bc7_encode_kernelILi512E, mip_fused_kernelILb1ELi1E) to pick its section.
 """
 import bisect, collections, csv, os, re, subprocess, sys, tempfile
 
 src_csv, obj, cu = sys.argv[1:4]
+want_section = sys.argv[4] if len(sys.argv) > 4 and not sys.argv[4].startswith("--") else None
+nlines = int(sys.argv[sys.argv.index("--lines") + 1]) if "--lines" in sys.argv else 25
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, capture_output=True)
 cubin = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
@@ -17,6 +21,8 @@ for line in sass.split("\n"):
         section = m.group(1)
         continue
     if not section or not section.startswith(".text."):
+        continue
+    if want_section and want_section not in section:
         continue
     m = re.search(r'//## File "([^"]+)", line (\d+)', line)
     if m:
@@ -65,5 +71,5 @@ for fn, v in sorted(agg.items(), key=lambda kv: -kv[1]["Instructions Executed"])
     ie = v["Instructions Executed"]
     print(f"{fn:24s} {v['static']:6d} {100*ie/tot:6.1f} {100*v['# Samples']/max(tots,1):6.1f} {v['stall_no_inst']:8d} {v['stall_wait']:7d} {v['stall_math']:7d} {v['stall_short_sb']:8d} {v['Thread Instructions Executed']/max(ie,1):6.1f}")
 print("hottest source lines (by samples):")
-for key, v in sorted(lines.items(), key=lambda kv: -kv[1]["# Samples"])[:25]:
+for key, v in sorted(lines.items(), key=lambda kv: -kv[1]["# Samples"])[:nlines]:
     print(f"  {key[0]}:{key[1]:<5d} samples {v['# Samples']:6d} inst {100*v['Instructions Executed']/tot:5.1f}%  no_inst {v['stall_no_inst']:5d}  | {text[key[1]-1].strip()[:90] if key[0]==os.path.basename(cu) else ''}")
