@@ -590,14 +590,27 @@ __device__ __forceinline__ void top_init(TopList& t) {
 #pragma unroll
     for (int k = 0; k < TOPK; k++) t.key[k] = 0xFFFFFFFFu;
 }
-__device__ __forceinline__ void top_insert(TopList& t, float score, int part) {
+// `keep` (uniform over the launch) = how many entries of the list the tier goes on to refine: the first `keep`
+// entries of the sorted insertion do not depend on the ones behind them, so those are not maintained
+__device__ __forceinline__ void top_insert(TopList& t, float score, int part, int keep) {
     score = score < 0.0f ? 0.0f : score;
     uint32_t key = (__float_as_uint(score) & ~63u) | (uint32_t)part;
-#pragma unroll
-    for (int k = 0; k < TOPK; k++) {
+    auto level = [&](int k) {
         const uint32_t lo = min(t.key[k], key);
         key = max(t.key[k], key);
         t.key[k] = lo;
+    };
+    level(0);
+    if (keep > 1) {
+        level(1);
+        if (keep > 2) {
+            level(2);
+            if (keep > 3) {
+                level(3);
+                level(4);
+                level(5);
+            }
+        }
     }
 }
 
@@ -634,7 +647,7 @@ __device__ __forceinline__ void masked_moments(const uint32_t pl[4][4], const ui
 // each list go to S.parts rows rowA.. and rowB.. (rowB < 0: second list not wanted).
 template <int NC, int NS, class SH>
 __device__ __forceinline__ void estimate_partitions(SH& S, int tid, int nparts, int ibA, int ibB,
-                                                    int rowA, int rowB) {
+                                                    int rowA, int rowB, int keepA, int keepB) {
     uint32_t pl[4][4];
 #pragma unroll
     for (int c = 0; c < 4; c++)
@@ -684,8 +697,8 @@ __device__ __forceinline__ void estimate_partitions(SH& S, int tid, int nparts, 
             A = A + tr_n;
             B = B + lam_n;
         }
-        top_insert(listA, A - kA * B, p);
-        top_insert(listB, A - kB * B, p);
+        top_insert(listA, A - kA * B, p, keepA);
+        if (rowB >= 0) top_insert(listB, A - kB * B, p, keepB);
     }
 #pragma unroll
     for (int k = 0; k < TOPK; k++) {
@@ -888,13 +901,15 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
         if (!on) continue;
         if (type == JOB_EST) {
             const int kind = (jw.y >> 11) & 3;
+            // w0 bits 2.. of an estimator job: entries of the first / second list that the tier refines
+            const int keepA = (jw.x >> 2) & 7, keepB = (jw.x >> 5) & 7;
             if (kind == 0)
-                estimate_partitions<3, 2>(S, tid, 64, 3, 2, 0 * TOPK, 1 * TOPK);
+                estimate_partitions<3, 2>(S, tid, 64, 3, 2, 0 * TOPK, 1 * TOPK, keepA, keepB);
             else if (kind == 3)
-                estimate_partitions<4, 2>(S, tid, 64, 2, 2, 4 * TOPK, -1);
+                estimate_partitions<4, 2>(S, tid, 64, 2, 2, 4 * TOPK, -1, keepA, 0);
             else
                 estimate_partitions<3, 3>(S, tid, kind == 1 ? 16 : 64, kind == 1 ? 3 : 2, 2,
-                                          kind == 1 ? 2 * TOPK : 3 * TOPK, -1);
+                                          kind == 1 ? 2 * TOPK : 3 * TOPK, -1, keepA, 0);
             continue;
         }
         Prep pr;
@@ -925,7 +940,31 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
             const uint32_t m1 = c_P3M1[partition], m2 = c_P3M2[partition];
             mask = k == 0 ? (0xFFFFu & ~(m1 | m2)) : (k == 1 ? m1 : m2);
         }
-        if (prep == PREP_COMPUTE || (prep == PREP_MODE6 && has_alpha)) {
+        Fit f;
+        // A scalar channel that is constant over the block (alpha of an opaque texture, R of a metallic-roughness map):
+        // prepare gives lo = hi = v (zero covariance, unit axis, mean v), the fit is q0 = q1 = Q(v) with every index 0
+        // and error 16 (v - E)^2, and the first least-squares round stops on det = 0.  Taken in closed form: same
+        // bits, none of the work (all scalar fits are without p-bits).
+        bool konst = false;
+        if (nc == 1) {
+            const uint32_t c4 = 4u * (pcmap & 15u);
+            const uint32_t w0 = S.pl[c4][tid];
+            const uint32_t v4 = __byte_perm(w0, 0u, 0x0000);
+            konst = w0 == v4 && S.pl[c4 + 1][tid] == v4 && S.pl[c4 + 2][tid] == v4 && S.pl[c4 + 3][tid] == v4;
+            if (konst) {
+                const int maxq = (1 << bits) - 1;
+                const int v = (int)(w0 & 255u);
+                const int q = quant_plain((float)v, (float)maxq / 255.0f, maxq);
+                const int d = v - expand_bits(q, bits);
+                f.q0 = f.q1 = (uint32_t)q;
+                f.pb = 0u;
+                f.idx = 0ull;
+                f.err = (uint32_t)(16 * d * d);
+            }
+        }
+        if (konst) {
+            // nothing to fit
+        } else if (prep == PREP_COMPUTE || (prep == PREP_MODE6 && has_alpha)) {
             if (nc == 4)
                 prepare<4>(S, tid, sel, pcmap, mask, pr);
             else if (nc == 3)
@@ -948,8 +987,7 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
                 pr.trace += 16 * 255 * 255;
             }
         }
-        Fit f;
-        refine(S, tid, c_VIEW_INV[view], pcmap, mask, ib, nc, bits, pbmode, ls, pbs, pr, f);
+        if (!konst) refine(S, tid, c_VIEW_INV[view], pcmap, mask, ib, nc, bits, pbmode, ls, pbs, pr, f);
         // ---- accumulate into the candidate ----
         if (first) {
 #pragma unroll
@@ -1085,15 +1123,16 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
         JobFields j = {JOB_FIT, mode, ns, k, prow, view, nc, ib, bits, pbmode, prep, first, last, areq, dest, idxsel, rot, 0};
         out[n++] = pack_job(j);
     };
-    auto est = [&](int kind, int areq) {
-        JobFields j = {JOB_EST, 0, 0, 0, 63, 0, 0, 0, 0, 0, 0, 0, 0, areq, 0, 0, 0, kind};
+    auto est = [&](int kind, int areq, int keepA, int keepB) {
+        // an estimator job carries the list lengths in the mode field (bits 2..4) and the ns | k fields (bits 5..7)
+        JobFields j = {JOB_EST, keepA, keepB & 3, (keepB >> 2) & 1, 63, 0, 0, 0, 0, 0, 0, 0, 0, areq, 0, 0, 0, kind};
         out[n++] = pack_job(j);
     };
     JobFields p3 = {JOB_PREP_P3, 0, 0, 0, 63, 1, 3, 0, 0, 0, 0, 0, 0, AREQ_ANY, 0, 0, 0, 0};
     out[n++] = pack_job(p3);
     fit(6, 1, 0, 63, 0, 4, 4, 7, PB_PER_EP, PREP_MODE6, 1, 1, AREQ_ANY, DEST_PART, 0, 0);
     if (t.n1 | t.n3) {
-        est(0, AREQ_OPAQUE);
+        est(0, AREQ_OPAQUE, t.n1 > 0 ? t.n1 : 1, t.n3 > 0 ? t.n3 : 1);
         for (int i = 0; i < t.n1; i++)
             for (int k = 0; k < 2; k++)
                 fit(1, 2, k, 0 * TOPK + i, 1, 3, 3, 6, PB_SHARED, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
@@ -1102,8 +1141,8 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
                 fit(3, 2, k, 1 * TOPK + i, 1, 3, 2, 7, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
     }
     if (t.n0 | t.n2) {
-        if (t.n0) est(1, AREQ_OPAQUE);
-        if (t.n2) est(2, AREQ_OPAQUE);
+        if (t.n0) est(1, AREQ_OPAQUE, t.n0, 0);
+        if (t.n2) est(2, AREQ_OPAQUE, t.n2, 0);
         for (int i = 0; i < t.n0; i++)
             for (int k = 0; k < 3; k++)
                 fit(0, 3, k, 2 * TOPK + i, 1, 3, 3, 4, PB_PER_EP, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
@@ -1112,7 +1151,7 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
                 fit(2, 3, k, 3 * TOPK + i, 1, 3, 2, 5, PB_NONE, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
     }
     if (t.n7) {
-        est(3, AREQ_ALPHA);
+        est(3, AREQ_ALPHA, t.n7, 0);
         for (int i = 0; i < t.n7; i++)
             for (int k = 0; k < 2; k++)
                 fit(7, 2, k, 4 * TOPK + i, 0, 4, 2, 5, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_ALPHA, DEST_PART, 0, 0);

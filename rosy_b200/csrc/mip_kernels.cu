@@ -292,6 +292,24 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
         "r"(parity), "r"(20000u)  // suspend-time hint, ns
         : "memory");
 }
+// The producer lane is three tiles ahead and has microseconds to spare: poll rarely, so that the polling does not
+// take issue slots from the consumers of its scheduler.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+    for (;;) {
+        uint32_t done;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (done) return;
+        __nanosleep(400);
+    }
+}
 __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int x, int y,
                                               uint64_t* bar) {
     asm volatile(
@@ -713,7 +731,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
             }
             const int lt = t - t_base;
             const int tile_x = lt % t_tiles_x, tile_y = lt / t_tiles_x;
-            if (it >= STAGES) mbar_wait_relaxed(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
+            if (it >= STAGES) mbar_wait_backoff(&S.empty[s], (uint32_t)((it / STAGES - 1) & 1));
             // the copy first: the barrier's phase cannot complete before the arrive below
             tma_load_tile(S.tiles[s], &T->tmap, tile_x * TILE, tile_y * TILE, &S.full[s]);
             TileInfo& I = S.info[it % INFO_RING];
@@ -982,12 +1000,22 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 // R (and G) of the sixteen re-normalised texels as raw samples, straight into the block encoder
                 constexpr int NCH = ENC == 1 ? 2 : 1;
                 uint32_t sr[16], sg[16];
+                if (normalize) {  // one uniform branch around the whole patch (inside the loop both sides get computed)
 #pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    normalize_texel_raw<NCH>(rows[r].x, normalize, sr[4 * r + 0], sg[4 * r + 0]);
-                    normalize_texel_raw<NCH>(rows[r].y, normalize, sr[4 * r + 1], sg[4 * r + 1]);
-                    normalize_texel_raw<NCH>(rows[r].z, normalize, sr[4 * r + 2], sg[4 * r + 2]);
-                    normalize_texel_raw<NCH>(rows[r].w, normalize, sr[4 * r + 3], sg[4 * r + 3]);
+                    for (int r = 0; r < 4; r++) {
+                        normalize_texel_raw<NCH>(rows[r].x, 1, sr[4 * r + 0], sg[4 * r + 0]);
+                        normalize_texel_raw<NCH>(rows[r].y, 1, sr[4 * r + 1], sg[4 * r + 1]);
+                        normalize_texel_raw<NCH>(rows[r].z, 1, sr[4 * r + 2], sg[4 * r + 2]);
+                        normalize_texel_raw<NCH>(rows[r].w, 1, sr[4 * r + 3], sg[4 * r + 3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 4; r++) {
+                        normalize_texel_raw<NCH>(rows[r].x, 0, sr[4 * r + 0], sg[4 * r + 0]);
+                        normalize_texel_raw<NCH>(rows[r].y, 0, sr[4 * r + 1], sg[4 * r + 1]);
+                        normalize_texel_raw<NCH>(rows[r].z, 0, sr[4 * r + 2], sg[4 * r + 2]);
+                        normalize_texel_raw<NCH>(rows[r].w, 0, sr[4 * r + 3], sg[4 * r + 3]);
+                    }
                 }
                 const uint32_t bi = I.borg[0] + (uint32_t)ty * (w0 >> 2) + (uint32_t)tx;
                 const uint2 rblk = bc45::alpha_block_raw<RAW_BASE>(sr, E.recip);
