@@ -339,7 +339,8 @@ __device__ __forceinline__ int evaluate(const SH& S, int tid, uint32_t inv, uint
                 best = __vimin3_s32(best, K[j] - (dp4a_uu(p, P[j], 0) << 5), K[j + 1] - (dp4a_uu(p, P[j + 1], 0) << 5));
             const int in = (int)m >> 31;  // all ones for a texel of the subset
             m <<= 1;
-            const int b = best & in;      // 16 * (|P|^2 - 2 p.P) + index; the low nibble survives the sign
+            // 4-bit indices only occur in mode 6, whose single subset is the whole block: no mask there
+            const int b = IB == 4 ? best : (best & in);  // 16 * (|P|^2 - 2 p.P) + index; the low nibble survives the sign
             total += b >> 4;
             acc = acc * 16u + ((uint32_t)b & 15u);
         }
@@ -419,6 +420,7 @@ __device__ __forceinline__ void refine(const SH& S, int tid, uint32_t inv, uint3
             const float kk = 64.0f / det;
 #pragma unroll
             for (int c = 0; c < 4; c++) {
+                if (c >= nc) break;  // uniform: channels outside the view stay zero (and are masked out of the end points)
                 const float fx = (float)(64 * P.S1[c] - Y[c]), fy = (float)Y[c];
                 P.lo[c] = clampf((fC * fx - fB * fy) * kk, 0.0f, 255.0f);
                 P.hi[c] = clampf((fA * fy - fB * fx) * kk, 0.0f, 255.0f);
@@ -488,6 +490,7 @@ __device__ __forceinline__ void refine(const SH& S, int tid, uint32_t inv, uint3
             if (!decided) {
 #pragma unroll
                 for (int c = 0; c < 4; c++) {
+                    if (c >= nc) break;  // uniform
                     int qa, qb, ea, eb;
                     if (pbmode == PB_NONE) {
                         qa = quant_plain(P.lo[c], scale, maxq);
@@ -590,27 +593,17 @@ __device__ __forceinline__ void top_init(TopList& t) {
 #pragma unroll
     for (int k = 0; k < TOPK; k++) t.key[k] = 0xFFFFFFFFu;
 }
-// `keep` (uniform over the launch) = how many entries of the list the tier goes on to refine: the first `keep`
-// entries of the sorted insertion do not depend on the ones behind them, so those are not maintained
-__device__ __forceinline__ void top_insert(TopList& t, float score, int part, int keep) {
+// KEEP = how many entries of the list are ever read: the first KEEP entries of the sorted insertion do not depend
+// on the ones behind them, so those are not maintained (fast / normal tiers refine at most 3 + 2 partitions)
+template <int KEEP>
+__device__ __forceinline__ void top_insert(TopList& t, float score, int part) {
     score = score < 0.0f ? 0.0f : score;
     uint32_t key = (__float_as_uint(score) & ~63u) | (uint32_t)part;
-    auto level = [&](int k) {
+#pragma unroll
+    for (int k = 0; k < KEEP; k++) {
         const uint32_t lo = min(t.key[k], key);
         key = max(t.key[k], key);
         t.key[k] = lo;
-    };
-    level(0);
-    if (keep > 1) {
-        level(1);
-        if (keep > 2) {
-            level(2);
-            if (keep > 3) {
-                level(3);
-                level(4);
-                level(5);
-            }
-        }
     }
 }
 
@@ -644,10 +637,11 @@ __device__ __forceinline__ void masked_moments(const uint32_t pl[4][4], const ui
 }
 
 // Rank the partitions of a 2- or 3-subset table for two index widths at once; the best TOPK of
-// each list go to S.parts rows rowA.. and rowB.. (rowB < 0: second list not wanted).
+// each list go to S.parts rows rowA.. and rowB.. (rowB < 0: second list not wanted).  `small` (uniform over
+// the launch): only the first 3 / 2 entries of the lists will be read.
 template <int NC, int NS, class SH>
 __device__ __forceinline__ void estimate_partitions(SH& S, int tid, int nparts, int ibA, int ibB,
-                                                    int rowA, int rowB, int keepA, int keepB) {
+                                                    int rowA, int rowB, bool small) {
     uint32_t pl[4][4];
 #pragma unroll
     for (int c = 0; c < 4; c++)
@@ -697,8 +691,13 @@ __device__ __forceinline__ void estimate_partitions(SH& S, int tid, int nparts, 
             A = A + tr_n;
             B = B + lam_n;
         }
-        top_insert(listA, A - kA * B, p, keepA);
-        if (rowB >= 0) top_insert(listB, A - kB * B, p, keepB);
+        if (small) {
+            top_insert<3>(listA, A - kA * B, p);
+            top_insert<2>(listB, A - kB * B, p);
+        } else {
+            top_insert<TOPK>(listA, A - kA * B, p);
+            top_insert<TOPK>(listB, A - kB * B, p);
+        }
     }
 #pragma unroll
     for (int k = 0; k < TOPK; k++) {
@@ -901,15 +900,13 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
         if (!on) continue;
         if (type == JOB_EST) {
             const int kind = (jw.y >> 11) & 3;
-            // w0 bits 2.. of an estimator job: entries of the first / second list that the tier refines
-            const int keepA = (jw.x >> 2) & 7, keepB = (jw.x >> 5) & 7;
             if (kind == 0)
-                estimate_partitions<3, 2>(S, tid, 64, 3, 2, 0 * TOPK, 1 * TOPK, keepA, keepB);
+                estimate_partitions<3, 2>(S, tid, 64, 3, 2, 0 * TOPK, 1 * TOPK, tier < 2);
             else if (kind == 3)
-                estimate_partitions<4, 2>(S, tid, 64, 2, 2, 4 * TOPK, -1, keepA, 0);
+                estimate_partitions<4, 2>(S, tid, 64, 2, 2, 4 * TOPK, -1, tier < 2);
             else
                 estimate_partitions<3, 3>(S, tid, kind == 1 ? 16 : 64, kind == 1 ? 3 : 2, 2,
-                                          kind == 1 ? 2 * TOPK : 3 * TOPK, -1, keepA, 0);
+                                          kind == 1 ? 2 * TOPK : 3 * TOPK, -1, false);
             continue;
         }
         Prep pr;
@@ -944,7 +941,7 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
         // A scalar channel that is constant over the block (alpha of an opaque texture, R of a metallic-roughness map):
         // prepare gives lo = hi = v (zero covariance, unit axis, mean v), the fit is q0 = q1 = Q(v) with every index 0
         // and error 16 (v - E)^2, and the first least-squares round stops on det = 0.  Taken in closed form: same
-        // bits, none of the work (all scalar fits are without p-bits).
+        // bits, none of the work (all scalar fits are without p-bits).  -1.6 % warp instructions on opaque textures.
         bool konst = false;
         if (nc == 1) {
             const uint32_t c4 = 4u * (pcmap & 15u);
@@ -963,7 +960,7 @@ __device__ __forceinline__ uint4 encode_texels(SH& S, const int tid, const bool 
             }
         }
         if (konst) {
-            // nothing to fit
+            // nothing to prepare
         } else if (prep == PREP_COMPUTE || (prep == PREP_MODE6 && has_alpha)) {
             if (nc == 4)
                 prepare<4>(S, tid, sel, pcmap, mask, pr);
@@ -1123,16 +1120,15 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
         JobFields j = {JOB_FIT, mode, ns, k, prow, view, nc, ib, bits, pbmode, prep, first, last, areq, dest, idxsel, rot, 0};
         out[n++] = pack_job(j);
     };
-    auto est = [&](int kind, int areq, int keepA, int keepB) {
-        // an estimator job carries the list lengths in the mode field (bits 2..4) and the ns | k fields (bits 5..7)
-        JobFields j = {JOB_EST, keepA, keepB & 3, (keepB >> 2) & 1, 63, 0, 0, 0, 0, 0, 0, 0, 0, areq, 0, 0, 0, kind};
+    auto est = [&](int kind, int areq) {
+        JobFields j = {JOB_EST, 0, 0, 0, 63, 0, 0, 0, 0, 0, 0, 0, 0, areq, 0, 0, 0, kind};
         out[n++] = pack_job(j);
     };
     JobFields p3 = {JOB_PREP_P3, 0, 0, 0, 63, 1, 3, 0, 0, 0, 0, 0, 0, AREQ_ANY, 0, 0, 0, 0};
     out[n++] = pack_job(p3);
     fit(6, 1, 0, 63, 0, 4, 4, 7, PB_PER_EP, PREP_MODE6, 1, 1, AREQ_ANY, DEST_PART, 0, 0);
     if (t.n1 | t.n3) {
-        est(0, AREQ_OPAQUE, t.n1 > 0 ? t.n1 : 1, t.n3 > 0 ? t.n3 : 1);
+        est(0, AREQ_OPAQUE);
         for (int i = 0; i < t.n1; i++)
             for (int k = 0; k < 2; k++)
                 fit(1, 2, k, 0 * TOPK + i, 1, 3, 3, 6, PB_SHARED, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
@@ -1141,8 +1137,8 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
                 fit(3, 2, k, 1 * TOPK + i, 1, 3, 2, 7, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_OPAQUE, DEST_PART, 0, 0);
     }
     if (t.n0 | t.n2) {
-        if (t.n0) est(1, AREQ_OPAQUE, t.n0, 0);
-        if (t.n2) est(2, AREQ_OPAQUE, t.n2, 0);
+        if (t.n0) est(1, AREQ_OPAQUE);
+        if (t.n2) est(2, AREQ_OPAQUE);
         for (int i = 0; i < t.n0; i++)
             for (int k = 0; k < 3; k++)
                 fit(0, 3, k, 2 * TOPK + i, 1, 3, 3, 4, PB_PER_EP, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
@@ -1151,7 +1147,7 @@ int build_jobs(const Bc7Tier& t, uint2* out) {
                 fit(2, 3, k, 3 * TOPK + i, 1, 3, 2, 5, PB_NONE, PREP_COMPUTE, k == 0, k == 2, AREQ_OPAQUE, DEST_PART, 0, 0);
     }
     if (t.n7) {
-        est(3, AREQ_ALPHA, t.n7, 0);
+        est(3, AREQ_ALPHA);
         for (int i = 0; i < t.n7; i++)
             for (int k = 0; k < 2; k++)
                 fit(7, 2, k, 4 * TOPK + i, 0, 4, 2, 5, PB_PER_EP, PREP_COMPUTE, k == 0, k == 1, AREQ_ALPHA, DEST_PART, 0, 0);
@@ -1212,6 +1208,8 @@ int bc7_upload_tables() {
     for (int t = 0; t < 3; t++) {
         njobs[t] = build_jobs(kTiers[t], jobs[t]);
         if (njobs[t] > MAXJOBS) return -1;
+        // the kernel keeps only 3 + 2 list entries below the high tier (estimate_partitions, `small`)
+        if (t < 2 && (kTiers[t].n1 > 3 || kTiers[t].n3 > 2 || kTiers[t].n7 > 3)) return -1;
     }
     cudaError_t e = cudaSuccess;
     auto ok = [&](cudaError_t r) {

@@ -49,30 +49,55 @@ static int paeth(int a, int b, int c) {
 }
 
 // undo the scanline filters of one (sub)image in place; returns false on a bad filter byte
-static bool png_unfilter(uint8_t* data, size_t w, size_t h, int bpp_bits) {
-    const size_t stride = (w * (size_t)bpp_bits + 7) / 8, bpp = (size_t)(bpp_bits + 7) / 8;
+// One row, filter type FT, BPP bytes per complete pixel (a compile-time constant for the common layouts so
+// that the left-neighbour distance is fixed and the loops unroll).  The file pipeline is decode-bound
+// (DESIGN.md section 5), so the row loops are kept free of per-byte dispatch.
+template <int FT, size_t BPP>
+static void png_unfilter_row(uint8_t* cur, const uint8_t* prev, size_t stride, size_t bpp_rt) {
+    const size_t bpp = BPP ? BPP : bpp_rt;
+    const size_t head = bpp < stride ? bpp : stride;
+    for (size_t i = 0; i < head; i++) {  // no left neighbour yet: a = c = 0
+        const int b = prev[i];
+        int v = cur[i];
+        if (FT == 2) v += b;
+        if (FT == 3) v += b >> 1;
+        if (FT == 4) v += paeth(0, b, 0);
+        cur[i] = (uint8_t)v;
+    }
+    for (size_t i = bpp; i < stride; i++) {
+        const int a = cur[i - bpp], b = prev[i], c = prev[i - bpp];
+        int v = cur[i];
+        if (FT == 1) v += a;
+        if (FT == 2) v += b;
+        if (FT == 3) v += (a + b) >> 1;
+        if (FT == 4) v += paeth(a, b, c);
+        cur[i] = (uint8_t)v;
+    }
+}
+template <size_t BPP>
+static bool png_unfilter_rows(uint8_t* data, size_t stride, size_t h, size_t bpp_rt) {
     std::vector<uint8_t> zero(stride, 0);
     const uint8_t* prev = zero.data();
     for (size_t y = 0; y < h; y++) {
         uint8_t* row = data + y * (stride + 1);
-        const int ft = row[0];
         uint8_t* cur = row + 1;
-        for (size_t i = 0; i < stride; i++) {
-            const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
-            int v = cur[i];
-            switch (ft) {
-                case 0: break;
-                case 1: v += a; break;
-                case 2: v += b; break;
-                case 3: v += (a + b) >> 1; break;
-                case 4: v += paeth(a, b, c); break;
-                default: return false;
-            }
-            cur[i] = (uint8_t)v;
+        switch (row[0]) {
+            case 0: break;
+            case 1: png_unfilter_row<1, BPP>(cur, prev, stride, bpp_rt); break;
+            case 2: png_unfilter_row<2, BPP>(cur, prev, stride, bpp_rt); break;
+            case 3: png_unfilter_row<3, BPP>(cur, prev, stride, bpp_rt); break;
+            case 4: png_unfilter_row<4, BPP>(cur, prev, stride, bpp_rt); break;
+            default: return false;
         }
         prev = cur;
     }
     return true;
+}
+static bool png_unfilter(uint8_t* data, size_t w, size_t h, int bpp_bits) {
+    const size_t stride = (w * (size_t)bpp_bits + 7) / 8, bpp = (size_t)(bpp_bits + 7) / 8;
+    if (bpp == 4) return png_unfilter_rows<4>(data, stride, h, bpp);
+    if (bpp == 3) return png_unfilter_rows<3>(data, stride, h, bpp);
+    return png_unfilter_rows<0>(data, stride, h, bpp);
 }
 
 static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba, uint32_t& W, uint32_t& H) {
@@ -174,8 +199,23 @@ static int decode_png(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
         const size_t stride = (pw * (size_t)bpp_bits + 7) / 8;
         uint8_t* sub = raw.data() + off;
         if (!png_unfilter(sub, pw, ph, bpp_bits)) return ROSY_TEX_ERR_DECODE;
+        // the two layouts almost every texture uses: 8-bit RGBA / RGB, not interlaced, no colour key
+        const bool fast = !interlace && depth == 8 && (ctype == 6 || (ctype == 2 && trns.size() < 6));
         for (size_t y = 0; y < ph; y++) {
             const uint8_t* row = sub + y * (stride + 1) + 1;
+            if (fast) {
+                uint8_t* o = &rgba[y * (size_t)w * 4];
+                if (ctype == 6) {
+                    memcpy(o, row, (size_t)w * 4);
+                } else {
+                    for (size_t x = 0; x < pw; x++) {
+                        o[4 * x] = row[3 * x];
+                        o[4 * x + 1] = row[3 * x + 1];
+                        o[4 * x + 2] = row[3 * x + 2];
+                    }  // alpha is already 255
+                }
+                continue;
+            }
             for (size_t x = 0; x < pw; x++) {
                 int s[4] = {0, 0, 0, 0};   // samples as 8-bit (16-bit: high byte, like stb_image)
                 int s16[4] = {0, 0, 0, 0};  // full samples for the tRNS colour key

@@ -32,5 +32,7 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "sizes":  # single-texture launches: the CTA size choice (ROSY_TEX_BC7_NT forces one)
         for n in (256, 512, 1024, 2048, 4096):
             run("albedo", 0, 1, n=n, reps=20 if n <= 1024 else 5)
+    elif len(sys.argv) > 1 and sys.argv[1] == "one":
+        run("albedo", 0, 1)
     else:
         run("albedo", 0, 1); run("albedo", 0, 0); run("albedo", 0, 2, reps=3); run("normal", 1, 1)
