@@ -211,6 +211,11 @@ constexpr int SRGB_BASE = (int)(SRGB_LO >> SRGB_SHIFT);
 constexpr int SRGB_ENTRIES = (int)((SRGB_HI - SRGB_LO) >> SRGB_SHIFT) + 1;
 
 __constant__ float2 c_SRGB_ENCODE[SRGB_ENTRIES];
+// the same tables in global memory for the fused kernel's prologue (per-lane indices: a coalesced load, where
+// constant memory would serialise)
+__device__ float2 g_SRGB_ENCODE[SRGB_ENTRIES];
+__device__ float g_SRGB_TO_LINEAR[256], g_UNORM8[256];
+static_assert(SRGB_ENTRIES <= 10 * 32, "the prologue of the fused kernel fills the encode table with ten warps");
 __constant__ volatile unsigned int* c_LAYOUT_FAULT;  // mapped host memory, set by a fused launch that found an unexpected shared window
 __constant__ float c_UNORM8[256];  // i / 255.0f, as nvtt::Surface::load produces it
 
@@ -666,15 +671,6 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
     const int first_tile = vblock * tiles_lo + (vblock < tiles_rem ? vblock : tiles_rem);
     const int tail_bar = 1 + grp;
 
-    if (!NORMAL) {
-        // each warp fills its share of the values, every value replicated across the 32 banks
-        for (int v = (int)(threadIdx.x >> 5); v < 256; v += NTHREADS_TOTAL * GROUPS / 32) {
-            lin_tab[v * 64 + lane] = (c_SRGB_TO_LINEAR[v] + SRGB_BIAS) * 0.25f;
-            lin_tab[v * 64 + 32 + lane] = c_UNORM8[v];
-        }
-        for (int i = threadIdx.x; i < SRGB_ENTRIES; i += NTHREADS_TOTAL * GROUPS) srgb_tab[i] = c_SRGB_ENCODE[i];
-    }
-    if (ENC && threadIdx.x < 256) E.recip[threadIdx.x] = bc45::g_RECIP20[threadIdx.x];
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
             mbar_init(&S.full[s], 1);
@@ -688,7 +684,29 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         S.nqueue = 0;
     }
-    __syncthreads();
+    __syncthreads();  // the barriers exist: the producers start their first copies now, under the table fill below
+
+    if (warp != 9) {
+        // ---- tables, by the 18 consumer / auxiliary warps; one coalesced global load per thread, no dependent chain
+        // of constant-cache misses (a single 2048^2 launch spent ~3 of its ~20 us here) ----
+        const int fw = grp * 9 + warp;  // 0..17
+        if (!NORMAL) {
+            if (fw < 8) {
+                // values 32 fw .. 32 fw + 31: lane k holds value 32 fw + k; every value is replicated across the 32 banks
+                const float lin = (g_SRGB_TO_LINEAR[32 * fw + lane] + SRGB_BIAS) * 0.25f, un = g_UNORM8[32 * fw + lane];
+#pragma unroll 8
+                for (int k = 0; k < 32; k++) {
+                    lin_tab[(32 * fw + k) * 64 + lane] = __shfl_sync(0xFFFFFFFFu, lin, k);
+                    lin_tab[(32 * fw + k) * 64 + 32 + lane] = __shfl_sync(0xFFFFFFFFu, un, k);
+                }
+            } else {
+                const int i = (fw - 8) * 32 + lane;  // 320 >= SRGB_ENTRIES
+                if (i < SRGB_ENTRIES) srgb_tab[i] = g_SRGB_ENCODE[i];
+            }
+        }
+        if (ENC && fw >= 10) E.recip[(fw - 10) * 32 + lane] = bc45::g_RECIP20[(fw - 10) * 32 + lane];
+        asm volatile("bar.sync 3, %0;" ::"n"((NTHREADS_TOTAL - 32) * GROUPS) : "memory");
+    }
 
     if (warp == 9) {
         // ================================ producer ================================
@@ -1440,7 +1458,10 @@ int mips_upload_tables() {
             }
         }
     }
-    return cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
+    return cudaMemcpyToSymbol(g_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
+                   cudaMemcpyToSymbol(g_UNORM8, unorm, sizeof unorm) == cudaSuccess &&
+                   cudaMemcpyToSymbol(g_SRGB_ENCODE, enc, sizeof enc) == cudaSuccess &&
+                   cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&
                    cudaMemcpyToSymbol(c_UNORM8, unorm, sizeof unorm) == cudaSuccess &&
                    cudaMemcpyToSymbol(c_SRGB_ENCODE, enc, sizeof enc) == cudaSuccess
                ? 0
