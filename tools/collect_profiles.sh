@@ -14,7 +14,7 @@ for k in bc7 mip bc5; do
 done
 if [ -f gpurun_out/${TAG}_bc7.ncu-rep ]; then
     ncu -i gpurun_out/${TAG}_bc7.ncu-rep --page source --csv > /tmp/${TAG}_bc7.src.csv 2>/dev/null
-    python tools/ncu_hot_functions.py /tmp/${TAG}_bc7.src.csv rosy_b200/csrc/bc7_encode.o rosy_b200/csrc/bc7_encode.cu > profiles/${TAG}_bc7_hot_functions.txt || true
+    python tools/ncu_hot_functions.py /tmp/${TAG}_bc7.src.csv rosy_b200/csrc/bc7_encode.o rosy_b200/csrc/bc7_encode.cu bc7_encode_kernelILi512E > profiles/${TAG}_bc7_hot_functions.txt || true
 fi
 for f in launches.csv bench.json bench_ref.json bench_bc5.json bench_bc4.json mapping.json; do
     [ -f gpurun_out/${TAG}_$f ] && cp gpurun_out/${TAG}_$f profiles/${TAG}_$f

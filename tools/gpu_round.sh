@@ -18,7 +18,8 @@ python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.js
 # the HBM-bound encoders (north_star kernel 3): same workload shape, normal maps to BC5 and metal-rough maps to BC4
 python bench.py --kind normal --format bc5 --no-cpu > $OUT/${TAG}_bench_bc5.json 2>> $OUT/${TAG}_bench.err; echo "bc5 rc=$?"
 python bench.py --kind metal_rough --format bc4 --no-cpu > $OUT/${TAG}_bench_bc4.json 2>> $OUT/${TAG}_bench.err; echo "bc4 rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:bc45_encode -s 3 -c 1 -f -o $OUT/${TAG}_bc5 python bench.py --kind normal --format bc5 --textures 8 --steps 1 --warmup 3 --no-cpu --no-e2e > $OUT/${TAG}_ncu4.log 2>&1
+# BC5: the fused mip + encode kernel (levels 0..4 are encoded inside mip_fused_kernel<NORMAL, 1>)
+ncu --set full --clock-control none --import-source on -k regex:mip_fused -s 3 -c 1 -f -o $OUT/${TAG}_bc5 python bench.py --kind normal --format bc5 --textures 8 --steps 1 --warmup 3 --no-cpu --no-e2e > $OUT/${TAG}_ncu4.log 2>&1
 echo "bc5 full rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:bc7_encode -s 3 -c 1 -f -o $OUT/${TAG}_bc7 $SHORT > $OUT/${TAG}_ncu2.log 2>&1
 echo "bc7 full rc=$?"
