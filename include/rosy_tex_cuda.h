@@ -186,6 +186,11 @@ ROSY_TEX_API void rosy_tex_free_host(void* p);
  * (NULL: legacy default stream).  Nothing synchronises; kernels are only enqueued.
  *   d_chain  : rosy_tex_chain_size() bytes.  Receives levels 1.. (and level 0 for normal maps,
  *              whose level 0 is re-normalised); for colour maps level 0 is read from d_rgba.
+ *              Exception: rosy_tex_encode_device / _batch_device with BOTH stages and a BC5 / BC4
+ *              target on extents that are multiples of 64: levels 0..4 are block-compressed inside
+ *              the mip kernel and never written, and only the channels the format stores are
+ *              meaningful in levels 5.. - treat d_chain as scratch there (rosy_tex_mips_device
+ *              always writes the complete chain).
  *   d_scratch: rosy_tex_device_scratch_size() bytes; its first 256 bytes must be zero before the
  *              first use (the kernels leave them zero again).
  *   d_blocks : rosy_tex_dds_size() - 148 bytes, every level's blocks, largest level first. */
