@@ -339,7 +339,11 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
 }
 template <int C>
 __device__ __forceinline__ float lin_lookup(uint32_t lanebase, uint32_t p) {
+#if defined(MIP_EXPERIMENT) && (MIP_EXPERIMENT & 2)
+    return (__uint_as_float(__byte_perm(p, 0x4B000000u, 0x7440 + C)) - 8388608.0f) * (0.25f / 255.0f) + 0.00048828125f;  // timing experiment: no table
+#else
     return lds_f32(__byte_perm(p, lanebase, 0x7604 + (C << 4)));
+#endif
 }
 __device__ __forceinline__ float alpha_lookup(uint32_t lanebase, uint32_t p) {
     return lds_f32(__byte_perm(p, lanebase, 0x7634) + 128u);
@@ -356,7 +360,30 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // the floored 8-bit value (no separate rounding step; the packing PRMTs pick byte 1).
 // c' must lie in [2^-9, 1 + 2^-9].
 constexpr float Q8_MAGIC = 32768.0f;
+//
+// Round 2: the table went.  Its 64-bit lookups at per-lane entries cost ~5 shared-memory wavefronts each (bank
+// conflicts) and were what held colour maps at 64 % of the HBM peak: without them the kernel runs at 89 %
+// (tools/mip_experiment.sh).  The transfer function is evaluated instead: two MUFU (lg2, ex2) and three
+// multiply-adds per value, ~2^-21 relative error = 0.0003 LSB (the table was good to 0.01), still no F2I.
+// MIP_SRGB_TABLE=1 builds the table version for A/B.
+#ifndef MIP_SRGB_TABLE
+#define MIP_SRGB_TABLE 0
+#endif
 __device__ __forceinline__ uint32_t srgb8_bits(float c, const float2* tab /* biased by SRGB_BASE */) {
+#if defined(MIP_EXPERIMENT) && (MIP_EXPERIMENT & 1)
+    return __float_as_uint(fmaf(c, 254.0f, 0.5f + Q8_MAGIC));  // timing experiment: no table
+#endif
+#if !MIP_SRGB_TABLE
+    // 255 toSrgb(c' - bias) + 0.5 + 2^15:  toSrgb(x) = 12.92 x below 0.0031308, 1.055 x^0.41666 - 0.055 above
+    // (Surface::toSrgb with NVTT-2's literal exponent); byte 1 of the result is the floored 8-bit value
+    const float x = c - SRGB_BIAS;
+    float l, e;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(l * 0.41666f));
+    const float hi = fmaf(e, 255.0f * 1.055f, Q8_MAGIC + 0.5f - 255.0f * 0.055f);
+    const float lo = fmaf(x, 255.0f * 12.92f, Q8_MAGIC + 0.5f);
+    return __float_as_uint(x <= 0.0031308f ? lo : hi);
+#endif
     const float2 t = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(tab) +
                                                       ((__float_as_uint(c) >> (SRGB_SHIFT - 3)) & 0x7FF8u));
     return __float_as_uint(fmaf(t.x, c, t.y));
