@@ -19,6 +19,8 @@ fi
 for f in launches.csv bench.json bench_ref.json bench_bc5.json bench_bc4.json mapping.json; do
     [ -f gpurun_out/${TAG}_$f ] && cp gpurun_out/${TAG}_$f profiles/${TAG}_$f
 done
+# the per-launch instruction counts bench.py's issue-slot roofline uses (keyed by the BC7 source hash)
+[ -f gpurun_out/${TAG}_bench_counts.json ] && cp gpurun_out/${TAG}_bench_counts.json profiles/bench_counts.json
 # SASS evidence per kernel: mnemonic histogram + the lines that prove TMA / mbarrier / dp4a
 {
     for o in mip_kernels bc7_encode bc45_encode; do
