@@ -434,6 +434,78 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
     return r;
 }
 
+// Two fp32 values in one 64-bit register: sm_100's FADD2 / FMUL2 / FFMA2 work on such pairs, one issue slot for two
+// results.  The normal-map arithmetic below runs on pairs of texels; every operation rounds exactly like its scalar
+// counterpart (fma.rm.f32x2 is the paired __fmaf_rd), so the results are those of the one-texel functions.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) {
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ f32x2 add2x(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2x(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 fma2x(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 fma2x_rd(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+// channel C of two texels as the floats 2^23 + 256 v + 128, minus 2^23 + 32768: 128 d, exact (see normalize_texel)
+template <int C>
+__device__ __forceinline__ f32x2 unpack_d2(uint32_t pa, uint32_t pb) {
+    return add2x(pk2(__uint_as_float(__byte_perm(pa, 0x4B000080u, 0x7504 + (C << 4))),
+                     __uint_as_float(__byte_perm(pb, 0x4B000080u, 0x7504 + (C << 4)))),
+                 pk2(-8421376.0f, -8421376.0f));
+}
+// Surface::normalizeNormalMap on two 8-bit texels at once; NCH = 3: R, G, B of both texels as the floats
+// 2^23 + v (raw samples, RAW_BASE + v); NCH = 1 / 2: R (and G) only, which is all the fused encode wants
+template <int NCH>
+__device__ __forceinline__ void normalize_pair(uint32_t pa, uint32_t pb, uint32_t ra[3], uint32_t rbv[3]) {
+    const f32x2 dx = unpack_d2<0>(pa, pb), dy = unpack_d2<1>(pa, pb), dz = unpack_d2<2>(pa, pb);
+    const f32x2 l2 = fma2x(dz, dz, fma2x(dy, dy, mul2x(dx, dx)));  // d is odd in every channel: never zero
+    float la, lb;
+    upk2(l2, la, lb);
+    const f32x2 s = mul2x(pk2(rsqrt_approx(la), rsqrt_approx(lb)), pk2(127.5f, 127.5f));
+    const f32x2 half = pk2(8388736.0f, 8388736.0f);
+    float a, b;
+    upk2(fma2x_rd(dx, s, half), a, b);
+    ra[0] = __float_as_uint(a);
+    rbv[0] = __float_as_uint(b);
+    if (NCH > 1) {
+        upk2(fma2x_rd(dy, s, half), a, b);
+        ra[1] = __float_as_uint(a);
+        rbv[1] = __float_as_uint(b);
+    }
+    if (NCH > 2) {
+        upk2(fma2x_rd(dz, s, half), a, b);
+        ra[2] = __float_as_uint(a);
+        rbv[2] = __float_as_uint(b);
+    }
+}
+// ... repacked as RGBA8, alpha passing through (level 0 of a normal map in the plain mip kernel)
+__device__ __forceinline__ void normalize_texels2(uint32_t& pa, uint32_t& pb) {
+    uint32_t a[3], b[3];
+    normalize_pair<3>(pa, pb, a, b);
+    pa = __byte_perm(__byte_perm(a[0], a[1], 0x0040), __byte_perm(a[2], pa, 0x0070), 0x5410);
+    pb = __byte_perm(__byte_perm(b[0], b[1], 0x0040), __byte_perm(b[2], pb, 0x0070), 0x5410);
+}
+
 // ---- normal maps ---------------------------------------------------------------------------
 // Surface::normalizeNormalMap on one 8-bit texel (level 0): d = 2 v - 255 exactly, n = d / |d|,
 // out = floor(127.5 n + 128) = floor(255 (n/2 + 1/2) + 0.5); alpha passes through.
@@ -509,6 +581,37 @@ __device__ __forceinline__ void finish_normal_sums_raw(uint32_t rb, uint32_t ga,
     const float s = l2 > 0.0f ? rsqrt_approx(l2) * 127.5f : 0.0f;
     r = __float_as_uint(__fmaf_rd(dx, s, 8388736.0f));
     if (NCH > 1) g = __float_as_uint(__fmaf_rd(dy, s, 8388736.0f));
+}
+
+// finish_normal_sums / finish_normal_sums_raw for two level-K texels at once (normalising case): R, G (, B) as raw
+// samples; same arithmetic as the one-texel functions, on FADD2 / FMUL2 / FFMA2
+template <int K, int NCH>
+__device__ __forceinline__ void finish_normal_sums_pair(uint32_t rb_a, uint32_t ga_a, uint32_t rb_b, uint32_t ga_b,
+                                                        uint32_t ra[3], uint32_t rbv[3]) {
+    constexpr float k2 = 8388608.0f + 255.0f * (float)(1 << (2 * K - 1));
+    const f32x2 mk2 = pk2(-k2, -k2);
+    const f32x2 dx = add2x(pk2(__uint_as_float(__byte_perm(rb_a, 0x4B000000u, 0x7410)), __uint_as_float(__byte_perm(rb_b, 0x4B000000u, 0x7410))), mk2);
+    const f32x2 dz = add2x(pk2(__uint_as_float(__byte_perm(rb_a, 0x4B000000u, 0x7432)), __uint_as_float(__byte_perm(rb_b, 0x4B000000u, 0x7432))), mk2);
+    const f32x2 dy = add2x(pk2(__uint_as_float(__byte_perm(ga_a, 0x4B000000u, 0x7410)), __uint_as_float(__byte_perm(ga_b, 0x4B000000u, 0x7410))), mk2);
+    const f32x2 l2 = fma2x(dz, dz, fma2x(dy, dy, mul2x(dx, dx)));
+    float la, lb;
+    upk2(l2, la, lb);
+    const float sa = la > 0.0f ? rsqrt_approx(la) * 127.5f : 0.0f, sb = lb > 0.0f ? rsqrt_approx(lb) * 127.5f : 0.0f;
+    const f32x2 s = pk2(sa, sb), half = pk2(8388736.0f, 8388736.0f);
+    float a, b;
+    upk2(fma2x_rd(dx, s, half), a, b);
+    ra[0] = __float_as_uint(a);
+    rbv[0] = __float_as_uint(b);
+    if (NCH > 1) {
+        upk2(fma2x_rd(dy, s, half), a, b);
+        ra[1] = __float_as_uint(a);
+        rbv[1] = __float_as_uint(b);
+    }
+    if (NCH > 2) {
+        upk2(fma2x_rd(dz, s, half), a, b);
+        ra[2] = __float_as_uint(a);
+        rbv[2] = __float_as_uint(b);
+    }
 }
 
 template <bool NORMAL>
@@ -1048,10 +1151,21 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 if (normalize) {  // one uniform branch around the whole patch (inside the loop both sides get computed)
 #pragma unroll
                     for (int r = 0; r < 4; r++) {
-                        normalize_texel_raw<NCH>(rows[r].x, 1, sr[4 * r + 0], sg[4 * r + 0]);
-                        normalize_texel_raw<NCH>(rows[r].y, 1, sr[4 * r + 1], sg[4 * r + 1]);
-                        normalize_texel_raw<NCH>(rows[r].z, 1, sr[4 * r + 2], sg[4 * r + 2]);
-                        normalize_texel_raw<NCH>(rows[r].w, 1, sr[4 * r + 3], sg[4 * r + 3]);
+                        uint32_t a[3], b[3];
+                        normalize_pair<NCH>(rows[r].x, rows[r].y, a, b);
+                        sr[4 * r + 0] = a[0];
+                        sr[4 * r + 1] = b[0];
+                        if (NCH > 1) {
+                            sg[4 * r + 0] = a[1];
+                            sg[4 * r + 1] = b[1];
+                        }
+                        normalize_pair<NCH>(rows[r].z, rows[r].w, a, b);
+                        sr[4 * r + 2] = a[0];
+                        sr[4 * r + 3] = b[0];
+                        if (NCH > 1) {
+                            sg[4 * r + 2] = a[1];
+                            sg[4 * r + 3] = b[1];
+                        }
                     }
                 } else {
 #pragma unroll
@@ -1075,10 +1189,8 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 for (int r = 0; r < 4; r++) {
                     uint4 o = rows[r];
                     if (normalize) {
-                        o.x = normalize_texel(o.x);
-                        o.y = normalize_texel(o.y);
-                        o.z = normalize_texel(o.z);
-                        o.w = normalize_texel(o.w);
+                        normalize_texels2(o.x, o.y);
+                        normalize_texels2(o.z, o.w);
                     }
                     c0[(size_t)r * (w0 / 4)] = o;
                 }
@@ -1096,11 +1208,30 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 const uint32_t ga_r = ((a.z >> 8) & 0x00FF00FFu) + ((a.w >> 8) & 0x00FF00FFu) +
                                       ((bq.z >> 8) & 0x00FF00FFu) + ((bq.w >> 8) & 0x00FF00FFu);
                 if (ENC) {
-                    finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_l, ga_l, normalize, l1r[2 * j], l1g[2 * j]);
-                    finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_r, ga_r, normalize, l1r[2 * j + 1], l1g[2 * j + 1]);
+                    if (normalize) {
+                        uint32_t a[3], bb[3];
+                        finish_normal_sums_pair<1, ENC == 1 ? 2 : 1>(rb_l, ga_l, rb_r, ga_r, a, bb);
+                        l1r[2 * j] = a[0];
+                        l1r[2 * j + 1] = bb[0];
+                        if (ENC == 1) {
+                            l1g[2 * j] = a[1];
+                            l1g[2 * j + 1] = bb[1];
+                        }
+                    } else {
+                        finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_l, ga_l, 0, l1r[2 * j], l1g[2 * j]);
+                        finish_normal_sums_raw<1, ENC == 1 ? 2 : 1>(rb_r, ga_r, 0, l1r[2 * j + 1], l1g[2 * j + 1]);
+                    }
+                } else if (normalize) {
+                    uint32_t a[3], bb[3];
+                    finish_normal_sums_pair<1, 3>(rb_l, ga_l, rb_r, ga_r, a, bb);
+                    // alpha = rounded mean, as in finish_normal_sums
+                    const uint32_t al = ((ga_l >> 16) + 2u) >> 2, ar = ((ga_r >> 16) + 2u) >> 2;
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
+                        make_uint2(__byte_perm(__byte_perm(a[0], a[1], 0x0040), __byte_perm(a[2], al, 0x0040), 0x5410),
+                                   __byte_perm(__byte_perm(bb[0], bb[1], 0x0040), __byte_perm(bb[2], ar, 0x0040), 0x5410));
                 } else {
                     *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
-                        make_uint2(finish_normal_sums<1>(rb_l, ga_l, normalize), finish_normal_sums<1>(rb_r, ga_r, normalize));
+                        make_uint2(finish_normal_sums<1>(rb_l, ga_l, 0), finish_normal_sums<1>(rb_r, ga_r, 0));
                 }
                 rb2 += rb_l + rb_r;
                 ga2 += ga_l + ga_r;
