@@ -575,6 +575,13 @@ def files_leg(T, images, kind, size):
                 p = os.path.join(d, f"t{i}.png")
                 Image.fromarray(img).save(p, compress_level=1)
             paths.append(p)
+        # three copies of every file: more files than host cores, so that the figure is the pipeline's throughput and
+        # not the latency of its slowest single decode
+        for p in list(paths):
+            for k in (1, 2):
+                q = os.path.join(d, f"c{k}_" + os.path.basename(p))
+                shutil.copyfile(p, q)
+                paths.append(q)
         in_bytes = sum(os.path.getsize(p) for p in paths)
         T.submit_file(paths[0], kind)  # warm-up: I/O threads, pinned pool
         T.wait_all()
@@ -585,7 +592,7 @@ def files_leg(T, images, kind, size):
         sec = time.perf_counter() - t0
         out_bytes = sum(os.path.getsize(os.path.splitext(p)[0] + ".dds") for p in paths)
         return {"value": len(paths) * size * size / 1e6 / sec, "unit": UNIT, "files": len(paths),
-                "formats": "PNG (even) / JPEG q90 (odd)", "input_file_bytes": in_bytes, "output_file_bytes": out_bytes,
+                "formats": "PNG / JPEG q90, half each", "input_file_bytes": in_bytes, "output_file_bytes": out_bytes,
                 "seconds": sec, "io_threads": int(os.environ.get("ROSY_TEX_IO_THREADS", os.cpu_count() or 1)),
                 "api": "rosy_tex_submit(path) + rosy_tex_wait_all: file decode and .dds write inside the timed region"}
     finally:
