@@ -401,7 +401,7 @@ static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
     // the payload must be able to hold the image before anything of its size is allocated
     const size_t avail = f.size() - pos;
     if (rle ? n > avail * 128 : n > avail / src_bytes) return ROSY_TEX_ERR_DECODE;
-    std::vector<uint8_t> px(n * comp);
+    std::vector<uint8_t> px;
     auto read_pixel = [&](const uint8_t* s, uint8_t* o) {
         if (cmap) {
             size_t idx = bpp == 8 ? s[0] : (size_t)(s[0] | (s[1] << 8));
@@ -409,10 +409,43 @@ static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
             memcpy(o, &pal[idx * comp], (size_t)comp);
         } else if (rgb16) {
             rgb555(s, o);
+        } else if (comp == 4) {
+            memcpy(o, s, 4);  // fixed sizes: the FBX route feeds 24- / 32-bit TGA only and a run-time-sized memcpy is a call
+        } else if (comp == 3) {
+            memcpy(o, s, 3);
         } else {
             memcpy(o, s, (size_t)comp);
         }
     };
+    const bool plain = !cmap && !rgb16 && (comp == 3 || comp == 4);
+    if (!rle && plain) {
+        // uncompressed true colour: straight from the file to RGBA8, one row at a time
+        W = w;
+        H = h;
+        rgba.resize(n * 4);
+        const bool top_first = desc & 0x20;
+        for (uint32_t y = 0; y < h; y++) {
+            const uint8_t* s = &f[pos + (size_t)(top_first ? y : h - 1 - y) * w * comp];
+            uint8_t* o = &rgba[(size_t)y * w * 4];
+            if (comp == 4) {
+                for (uint32_t x = 0; x < w; x++) {
+                    uint32_t v;
+                    memcpy(&v, s + 4 * (size_t)x, 4);
+                    v = (v & 0xFF00FF00u) | ((v >> 16) & 0xFFu) | ((v & 0xFFu) << 16);  // BGRA -> RGBA
+                    memcpy(o + 4 * (size_t)x, &v, 4);
+                }
+            } else {
+                for (uint32_t x = 0; x < w; x++) {
+                    o[4 * (size_t)x] = s[3 * (size_t)x + 2];
+                    o[4 * (size_t)x + 1] = s[3 * (size_t)x + 1];
+                    o[4 * (size_t)x + 2] = s[3 * (size_t)x];
+                    o[4 * (size_t)x + 3] = 255;
+                }
+            }
+        }
+        return ROSY_TEX_OK;
+    }
+    px.resize(n * comp);
     if (!rle) {
         for (size_t i = 0; i < n; i++) read_pixel(&f[pos + i * src_bytes], &px[i * comp]);
     } else {
@@ -445,6 +478,15 @@ static int decode_tga(const std::vector<uint8_t>& f, std::vector<uint8_t>& rgba,
         const size_t sy = top ? y : h - 1 - y;
         const uint8_t* s = &px[sy * w * comp];
         uint8_t* o = &rgba[(size_t)y * w * 4];
+        if (plain && comp == 4) {
+            for (uint32_t x = 0; x < w; x++) {
+                uint32_t v;
+                memcpy(&v, s + 4 * (size_t)x, 4);
+                v = (v & 0xFF00FF00u) | ((v >> 16) & 0xFFu) | ((v & 0xFFu) << 16);
+                memcpy(o + 4 * (size_t)x, &v, 4);
+            }
+            continue;
+        }
         for (uint32_t x = 0; x < w; x++, s += comp, o += 4) {
             if (comp <= 2) {
                 o[0] = o[1] = o[2] = s[0];
