@@ -223,6 +223,11 @@ ROSY_TEX_API int rosy_tex_encode_batch_device(const rosy_tex_batch_item* items, 
                                               void* d_batch_scratch, void* stream, int do_mips,
                                               int do_blocks);
 
+/* Debug aid: a library built with `make -C rosy_b200/csrc checked` tests every global store of the warp-specialised mip
+ * (+ BC5 / BC4) kernel against the extent of its buffer and counts the violations; this returns the count over the
+ * devices in use.  The product build returns -1. */
+ROSY_TEX_API long long rosy_tex_debug_faults(void);
+
 /* number of kernels this library has launched since load (all threads, all devices) */
 ROSY_TEX_API uint64_t rosy_tex_kernel_launches(void);
 

@@ -237,6 +237,7 @@ struct alignas(64) MipTex {
     uint8_t* blocks;       // fused encode (ENC != 0): the texture's block stream; levels 0..4 are encoded here
     uint32_t lblk[FUSED_ENC_LEVELS];  // first block of levels 0..4 in that stream
     uint32_t pad2;
+    uint64_t chain_bytes, block_bytes, top_bytes;  // extents of chainbuf / blocks / tile_top..tail_b (ROSY_TEX_CHECKED builds test every store)
     uint32_t lw[ROSY_TEX_MAX_LEVELS], lh[ROSY_TEX_MAX_LEVELS];
     uint64_t lpx[ROSY_TEX_MAX_LEVELS];  // px_offset per level
 };
@@ -254,7 +255,34 @@ struct TileInfo {
     uint32_t org[4];  // pixel index of this tile's first texel in levels 0..3 (off[l] included)
     uint8_t* blocks;  // fused encode: the block stream and the index of this tile's first block in levels 0..4
     uint32_t borg[FUSED_ENC_LEVELS];
+#ifdef ROSY_TEX_CHECKED
+    uint64_t chain_bytes, block_bytes;
+    const uint8_t* top_base;
+    uint64_t top_bytes;
+#endif
 };
+
+// ROSY_TEX_CHECKED builds (make -C rosy_b200/csrc checked): every global store of the kernels in this file is tested
+// against the extent of the buffer it belongs to; violations are counted (the store still happens: the point is detection; compute-sanitizer is closed on the measurement pool).  rosy_tex_debug_faults() reads the count.
+#ifdef ROSY_TEX_CHECKED
+__device__ unsigned int g_check_faults = 0;
+__device__ __forceinline__ void chk_store(const void* p, size_t n, const void* base, size_t limit) {
+    const uint8_t* q = static_cast<const uint8_t*>(p);
+    const uint8_t* b = static_cast<const uint8_t*>(base);
+    if (q < b || (size_t)(q - b) + n > limit) atomicAdd(&g_check_faults, 1u);
+}
+#define CHK_CHAIN(I_, p, n) chk_store((p), (n), (I_).chainbuf, (I_).chain_bytes)
+#define CHK_BLOCKS(I_, p, n) chk_store((p), (n), (I_).blocks, (I_).block_bytes)
+#define CHK_TOP(I_, p, n) chk_store((p), (n), (I_).top_base, (I_).top_bytes)
+#define CHK_T_CHAIN(T_, p, n) chk_store((p), (n), (T_)->chainbuf, (T_)->chain_bytes)
+#define CHK_T_TOP(T_, p, n) chk_store((p), (n), (T_)->tile_top, (T_)->top_bytes)
+#else
+#define CHK_CHAIN(I_, p, n) ((void)0)
+#define CHK_BLOCKS(I_, p, n) ((void)0)
+#define CHK_TOP(I_, p, n) ((void)0)
+#define CHK_T_CHAIN(T_, p, n) ((void)0)
+#define CHK_T_TOP(T_, p, n) ((void)0)
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -632,7 +660,7 @@ __device__ __forceinline__ void tail_sync(int bar_id) {
 }
 
 template <bool NORMAL, int NT, bool GSRC, bool GDST>
-__device__ __forceinline__ void tail_level(const float4* src, int sw, int sh, float4* dst, uint32_t* out,
+__device__ __forceinline__ void tail_level(const MipTex* T, const float4* src, int sw, int sh, float4* dst, uint32_t* out,
                                            int ow, int oh, int normalize, const float2* tab, int tid) {
     for (int o = tid; o < ow * oh; o += NT) {
         const int x = o % ow, y = o / ow;
@@ -648,10 +676,13 @@ __device__ __forceinline__ void tail_level(const float4* src, int sw, int sh, fl
             }
             acc = fma4(wy[j], row, acc);
         }
-        if (GDST)
+        if (GDST) {
+            CHK_T_TOP(T, dst + o, 16);
             __stcg(dst + o, acc);
-        else
+        } else {
             dst[o] = acc;
+        }
+        CHK_T_CHAIN(T, out + o, 4);
         out[o] = finish_any<NORMAL>(acc, normalize, tab);
     }
 }
@@ -668,7 +699,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     // levels too large for shared memory go through global scratch (L2)
     for (; l < levels && (int)(T->lw[l] * T->lh[l]) > TAIL_SMEM_PX; l++) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
-        tail_level<NORMAL, NT, true, true>(gsrc, sw, sh, gdst, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_level<NORMAL, NT, true, true>(T, gsrc, sw, sh, gdst, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
         tail_sync<NT>(bar_id);
         gsrc = gdst;
         gdst = (gdst == T->tail_a) ? T->tail_b : T->tail_a;
@@ -677,7 +708,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     }
     if (l < levels) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
-        tail_level<NORMAL, NT, true, false>(gsrc, sw, sh, sA, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_level<NORMAL, NT, true, false>(T, gsrc, sw, sh, sA, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
         tail_sync<NT>(bar_id);
         sw = ow;
         sh = oh;
@@ -686,7 +717,7 @@ __device__ __noinline__ void run_tail(const MipTex* T, float4* sA, float4* sB, c
     float4 *s = sA, *d = sB;
     for (; l < levels; l++) {
         const int ow = (int)T->lw[l], oh = (int)T->lh[l];
-        tail_level<NORMAL, NT, false, false>(s, sw, sh, d, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
+        tail_level<NORMAL, NT, false, false>(T, s, sw, sh, d, chain32 + T->lpx[l], ow, oh, normalize, tab, tid);
         tail_sync<NT>(bar_id);
         float4* t = s;
         s = d;
@@ -736,7 +767,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // r / g: the lane's raw samples (RAW_BASE + v), order (0,0) (0,1) (1,0) (1,1)
 template <int ENC>
 __device__ __forceinline__ void encode_quad_block_raw(const uint32_t r[4], const uint32_t g[4], const uint32_t* recip, int dx, int dy,
-                                                      uint8_t* blocks, uint32_t bi) {
+                                                      const TileInfo& I, uint32_t bi) {
+    uint8_t* const blocks = I.blocks;
     const int q = dx | (dy << 1);
     uint32_t rg[4];
 #pragma unroll
@@ -746,8 +778,10 @@ __device__ __forceinline__ void encode_quad_block_raw(const uint32_t r[4], const
     if (ENC == 1) {
         const uint2 gblk = bc45::alpha_block_quad<1>(rg, mm, recip, dx, dy);
         const uint32_t word = q == 0 ? rblk.x : (q == 1 ? rblk.y : (q == 2 ? gblk.x : gblk.y));
+        CHK_BLOCKS(I, blocks + (size_t)bi * 16 + 4 * q, 4);
         reinterpret_cast<uint32_t*>(blocks + (size_t)bi * 16)[q] = word;
     } else if (dy == 0) {
+        CHK_BLOCKS(I, blocks + (size_t)bi * 8 + 4 * q, 4);
         reinterpret_cast<uint32_t*>(blocks + (size_t)bi * 8)[q] = dx ? rblk.y : rblk.x;
     }
 }
@@ -895,6 +929,12 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
 #pragma unroll
             for (int l = 0; l < 4; l++)
                 I.org[l] = t_off[l] + (uint32_t)(tile_y * (TILE >> l)) * (t_w >> l) + (uint32_t)(tile_x * (TILE >> l));
+#ifdef ROSY_TEX_CHECKED
+            I.chain_bytes = T->chain_bytes;
+            I.block_bytes = T->block_bytes;
+            I.top_base = reinterpret_cast<const uint8_t*>(T->tile_top);
+            I.top_bytes = T->top_bytes;
+#endif
             if (ENC) {
                 I.blocks = t_blocks;
 #pragma unroll
@@ -1064,22 +1104,39 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                     const uint2 rblk = bc45::alpha_block(r4, E.recip);
                     if (ENC == 1) {
                         const uint2 gblk = bc45::alpha_block(g4, E.recip);
+                        CHK_BLOCKS(I, I.blocks + (size_t)bi * 16, 16);
                         *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
                     } else {
+                        CHK_BLOCKS(I, I.blocks + (size_t)bi * 8, 8);
                         *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
                     }
                 }
             } else {
+                CHK_CHAIN(I, c3a, 4);
+                CHK_CHAIN(I, c3b, 4);
                 *c3a = px3a;
                 *c3b = px3b;
             }
             if (role == 4) {
-                if (!ENC) chain32[I.off[4] + (size_t)(I.tile_y * 4 + (Ya >> 1) + (useB ? 2 : 0)) * w4 + I.tile_x * 4 + (X >> 1)] = pxc;
+                if (!ENC) {
+                    uint32_t* p4 = chain32 + (I.off[4] + (size_t)(I.tile_y * 4 + (Ya >> 1) + (useB ? 2 : 0)) * w4 + I.tile_x * 4 + (X >> 1));
+                    CHK_CHAIN(I, p4, 4);
+                    *p4 = pxc;
+                }
             } else if (role == 5)
-                chain32[I.off[5] + (size_t)(I.tile_y * 2 + (useB ? 1 : 0)) * w5 + I.tile_x * 2 + (X >> 2)] = pxc;
+{
+                uint32_t* p5 = chain32 + (I.off[5] + (size_t)(I.tile_y * 2 + (useB ? 1 : 0)) * w5 + I.tile_x * 2 + (X >> 2));
+                CHK_CHAIN(I, p5, 4);
+                *p5 = pxc;
+            }
             else if (role == 6) {
-                chain32[I.off[6] + (size_t)I.tile_y * w6 + I.tile_x] = pxc;
-                if (has_tail) __stcg(I.tile_top, v6);
+                uint32_t* p6 = chain32 + (I.off[6] + (size_t)I.tile_y * w6 + I.tile_x);
+                CHK_CHAIN(I, p6, 4);
+                *p6 = pxc;
+                if (has_tail) {
+                    CHK_TOP(I, I.tile_top, 16);
+                    __stcg(I.tile_top, v6);
+                }
             }
             // ticket bookkeeping is warp-uniform (every lane reads the same TileInfo); the boss lane acts
             int overflow_tex = -1;
@@ -1180,9 +1237,11 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 const uint2 rblk = bc45::alpha_block_raw<RAW_BASE>(sr, E.recip);
                 if (ENC == 1) {
                     const uint2 gblk = bc45::alpha_block_raw<RAW_BASE>(sg, E.recip);
-                    *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
+                    CHK_BLOCKS(I, I.blocks + (size_t)bi * 16, 16);
+                        *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
                 } else {
-                    *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
+                    CHK_BLOCKS(I, I.blocks + (size_t)bi * 8, 8);
+                        *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
                 }
             } else {
 #pragma unroll
@@ -1192,6 +1251,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                         normalize_texels2(o.x, o.y);
                         normalize_texels2(o.z, o.w);
                     }
+                    CHK_CHAIN(I, c0 + (size_t)r * (w0 / 4), 16);
                     c0[(size_t)r * (w0 / 4)] = o;
                 }
             }
@@ -1226,10 +1286,12 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                     finish_normal_sums_pair<1, 3>(rb_l, ga_l, rb_r, ga_r, a, bb);
                     // alpha = rounded mean, as in finish_normal_sums
                     const uint32_t al = ((ga_l >> 16) + 2u) >> 2, ar = ((ga_r >> 16) + 2u) >> 2;
+                    CHK_CHAIN(I, c1 + (size_t)j * w1, 8);
                     *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
                         make_uint2(__byte_perm(__byte_perm(a[0], a[1], 0x0040), __byte_perm(a[2], al, 0x0040), 0x5410),
                                    __byte_perm(__byte_perm(bb[0], bb[1], 0x0040), __byte_perm(bb[2], ar, 0x0040), 0x5410));
                 } else {
+                    CHK_CHAIN(I, c1 + (size_t)j * w1, 8);
                     *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) =
                         make_uint2(finish_normal_sums<1>(rb_l, ga_l, 0), finish_normal_sums<1>(rb_r, ga_r, 0));
                 }
@@ -1240,8 +1302,9 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                 uint32_t r2, g2 = 0u;
                 finish_normal_sums_raw<2, ENC == 1 ? 2 : 1>(rb2, ga2, normalize, r2, g2);
                 px2 = __byte_perm(r2, g2, 0x0040);  // R | G << 8
-                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
+                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
             } else {
+                CHK_CHAIN(I, c2, 4);
                 *c2 = finish_normal_sums<2>(rb2, ga2, normalize);
             }
             if (it >= L3_BUFS) mbar_wait(&S.l3empty[b], (uint32_t)((it / L3_BUFS - 1) & 1));
@@ -1271,8 +1334,10 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                     const uint2 rblk = bc45::alpha_block_raw<RAW_BASE>(sr, E.recip);
                     if (ENC == 1) {
                         const uint2 gblk = bc45::alpha_block_raw<RAW_BASE>(sg, E.recip);
+                        CHK_BLOCKS(I, I.blocks + (size_t)bi * 16, 16);
                         *reinterpret_cast<uint4*>(I.blocks + (size_t)bi * 16) = make_uint4(rblk.x, rblk.y, gblk.x, gblk.y);
                     } else {
+                        CHK_BLOCKS(I, I.blocks + (size_t)bi * 8, 8);
                         *reinterpret_cast<uint2*>(I.blocks + (size_t)bi * 8) = rblk;
                     }
                 }
@@ -1323,7 +1388,7 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                     finish_colour_raw<NCH>(v2, tab, r2, g2);
                 }
                 px2 = __byte_perm(r2, g2, 0x0040);  // R | G << 8
-                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I.blocks, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
+                encode_quad_block_raw<ENC>(l1r, l1g, E.recip, qdx, qdy, I, I.borg[1] + (uint32_t)(ty >> 1) * (w0 >> 3) + (uint32_t)(tx >> 1));
             } else {
                 if (opaque) {
                     float2 srg = make_float2(0.f, 0.f);
@@ -1344,9 +1409,11 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                             srg = add2(srg, rg);
                             sb += b_;
                         }
-                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                        CHK_CHAIN(I, c1 + (size_t)j * w1, 8);
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
                     }
                     v2 = make_float4(srg.x * 0.25f, srg.y * 0.25f, sb * 0.25f, 1.0f);
+                    CHK_CHAIN(I, c2, 4);
                     *c2 = finish_opaque(v2.x, v2.y, v2.z, tab);
                 } else {
                     float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1370,9 +1437,11 @@ mip_fused_kernel(const __grid_constant__ MipTex single, const MipTex* __restrict
                             o[i] = finish_colour(q, tab);
                             sum = add4(sum, q);
                         }
-                        *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
+                        CHK_CHAIN(I, c1 + (size_t)j * w1, 8);
+                    *reinterpret_cast<uint2*>(c1 + (size_t)j * w1) = make_uint2(o[0], o[1]);
                     }
                     v2 = scale4(sum, 0.25f);
+                    CHK_CHAIN(I, c2, 4);
                     *c2 = finish_colour(v2, tab);
                 }
             }
@@ -1451,7 +1520,7 @@ int force_generic() {
 
 // describe one texture for the fused kernel; false if the tensor map cannot be built
 bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba, uint8_t* d_chain,
-                 void* d_scratch, int tile_base, uint8_t* d_blocks = nullptr) {
+                 void* d_scratch, int tile_base, uint8_t* d_blocks = nullptr, int enc_block_bytes = 0) {
     memset(&T, 0, sizeof T);
     const cuuint64_t dims[2] = {c.lv[0].w, c.lv[0].h};
     const cuuint64_t strides[1] = {(cuuint64_t)c.lv[0].w * 4};
@@ -1477,6 +1546,14 @@ bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba
     T.tail_b = T.tail_a + ntiles;
     T.blocks = d_blocks;
     for (int l = 0; l < FUSED_ENC_LEVELS && l < c.levels; l++) T.lblk[l] = (uint32_t)c.lv[l].blk_offset;
+    T.chain_bytes = 4ull * c.total_px;
+    T.block_bytes = (uint64_t)c.total_blocks * (enc_block_bytes ? enc_block_bytes : 16);
+    T.top_bytes = 3ull * ntiles * sizeof(float4);
+#ifdef ROSY_TEX_CHECKED
+    // negative control of the checker: pretend the chain buffer is 4 KB shorter, so that the smallest levels' stores count as faults
+    if (const char* e = getenv("ROSY_TEX_CHECK_SELFTEST"))
+        if (atoi(e) && T.chain_bytes > 4096) T.chain_bytes -= 4096;
+#endif
     for (int l = 0; l < c.levels; l++) {
         T.lw[l] = c.lv[l].w;
         T.lh[l] = c.lv[l].h;
@@ -1525,6 +1602,17 @@ int fuse_encode_enabled() {
 }
 
 }  // namespace
+
+// ROSY_TEX_CHECKED builds: stores outside their buffers seen so far by the kernels of this file on the current device (-1: not a checked build)
+long long mips_check_faults() {
+#ifdef ROSY_TEX_CHECKED
+    unsigned int n = 0;
+    if (cudaMemcpyFromSymbol(&n, g_check_faults, sizeof n) != cudaSuccess) return -2;
+    return (long long)n;
+#else
+    return -1;
+#endif
+}
 
 // true once a fused launch on the current device has refused to run (unexpected shared-window layout)
 bool mips_layout_fault() {
@@ -1674,7 +1762,7 @@ int launch_mips(const Chain& c, bool normal_map, int normalize, const uint8_t* d
     if (fused_ok(c) && !force_generic() && get_encode_tiled()) {
         const int enc = d_blocks && mips_fused_encode_levels(c, enc_format) ? (enc_format == ROSY_TEX_FORMAT_BC5 ? 1 : 2) : 0;
         MipTex T;
-        if (!fill_miptex(T, c, normalize, d_rgba, d_chain, d_scratch, 0, enc ? d_blocks : nullptr)) return -1;
+        if (!fill_miptex(T, c, normalize, d_rgba, d_chain, d_scratch, 0, enc ? d_blocks : nullptr, enc == 2 ? 8 : 16)) return -1;
         const int ntiles = T.tiles_x * T.tiles_y;
         return launch_fused(normal_map, enc, &T, nullptr, nullptr, 1, ntiles, s) == cudaSuccess ? 1 : -1;
     }
@@ -1702,7 +1790,7 @@ int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream
             const int it_enc = it.d_blocks && mips_fused_encode_levels(it.chain, it.enc_format) ? (it.enc_format == ROSY_TEX_FORMAT_BC5 ? 1 : 2) : 0;
             if (it_enc != enc) continue;
             MipTex T;
-            if (!fill_miptex(T, it.chain, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, total, enc ? it.d_blocks : nullptr)) return -1;
+            if (!fill_miptex(T, it.chain, it.normalize, it.d_rgba, it.d_chain, it.d_scratch, total, enc ? it.d_blocks : nullptr, enc == 2 ? 8 : 16)) return -1;
             base.push_back(total);
             total += T.tiles_x * T.tiles_y;
             texs.push_back(T);

@@ -12,6 +12,7 @@
 #include <atomic>
 #include <condition_variable>
 #include <deque>
+#include <algorithm>
 #include <mutex>
 #include <new>
 #include <stdexcept>
@@ -1244,6 +1245,33 @@ static int encode_batch_device_impl(const rosy_tex_batch_item* items, int count,
 }
 
 extern "C" {
+long long rosy_tex_debug_faults(void) {
+    // stores outside their buffers counted by a ROSY_TEX_CHECKED build on every device in use; -1: not a checked build
+    State& s = st();
+    long long total = 0;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    std::vector<int> devs;
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        for (const Slot& sl : s.slots)
+            if (std::find(devs.begin(), devs.end(), sl.device) == devs.end()) devs.push_back(sl.device);
+    }
+    if (devs.empty()) devs.push_back(prev);
+    for (int d : devs) {
+        cudaSetDevice(d);
+        cudaDeviceSynchronize();
+        const long long n = mips_check_faults();
+        if (n < 0) {
+            cudaSetDevice(prev);
+            return n;
+        }
+        total += n;
+    }
+    cudaSetDevice(prev);
+    return total;
+}
+
 uint64_t rosy_tex_kernel_launches(void) { return g_launches.load(); }
 
 }  // extern "C"

@@ -86,6 +86,7 @@ size_t bc7_batch_desc_bytes(int n);
 int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_t s);
 int bc7_upload_tables();   // per device, once
 int mips_upload_tables();  // per device, once (also probes the shared-window layout the fused mip kernel needs)
-bool mips_layout_fault();  // a fused mip launch on the current device refused to run: its output is invalid
+bool mips_layout_fault();
+long long mips_check_faults();  // ROSY_TEX_CHECKED builds: out-of-bounds stores counted so far on the current device; -1 otherwise  // a fused mip launch on the current device refused to run: its output is invalid
 
 }  // namespace rosy_tex

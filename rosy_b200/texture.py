@@ -90,6 +90,7 @@ def lib():
         L.rosy_tex_chain_size.restype = C.c_size_t
         L.rosy_tex_device_scratch_size.restype = C.c_size_t
         L.rosy_tex_kernel_launches.restype = C.c_uint64
+        L.rosy_tex_debug_faults.restype = C.c_longlong
         L.rosy_tex_alloc_host.restype = C.c_void_p
         L.rosy_tex_alloc_host.argtypes = [C.c_size_t]
         L.rosy_tex_free_host.argtypes = [C.c_void_p]
@@ -304,6 +305,11 @@ def make_batch(entries):
 
 def encode_batch_device(batch, batch_scratch_ptr, stream=0, do_mips=True, do_blocks=True):
     _check(lib().rosy_tex_encode_batch_device(batch, len(batch), batch_scratch_ptr, stream, int(do_mips), int(do_blocks)))
+
+
+def debug_faults():
+    """out-of-bounds stores counted by a `make checked` build of the library; -1 for the product build"""
+    return lib().rosy_tex_debug_faults()
 
 
 def kernel_launches():
