@@ -204,6 +204,40 @@ ROSY_TEX_API int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d
                                         void* d_chain, void* d_scratch, void* d_blocks,
                                         void* stream);
 
+/* ---- the mip chain without any allocation ----------------------------------------------------
+ * No counterpart in the reference (NVTT allocates whatever it likes inside Surface::buildNextMipmap).
+ *
+ * Same result as rosy_tex_mips_device - the complete RGBA8 chain in d_chain, d_rgba / d_chain / stream exactly as
+ * described above - but the caller brings no scratch buffer and the library asks nobody for one: the fp32 hand-over
+ * buffers between levels live in a fixed array compiled into the library.  Neither this call nor anything it reaches
+ * uses cudaMalloc, cudaFree, cudaHostAlloc or any other allocator.
+ *
+ * Who needs that: code embedded in a host that has already handed the whole of device memory to its own arena (a
+ * game or render engine, a caching tensor allocator) and forbids plug-ins to go to the driver for more - there
+ * cudaMalloc simply fails; and code on a frame or streaming thread that must never stall, because cudaMalloc and
+ * cudaFree can make the whole device wait, whatever streams other threads are running.
+ *
+ * What it costs and where it stops:
+ *   - the array is ROSY_TEX_STATIC_SCRATCH_BYTES (5 MiB + 256) of device memory on EVERY GPU the process touches
+ *     with this library loaded, held until the process exits, used or not;
+ *   - a texture is accepted when levels 1 and 2 of its chain, as fp32 RGBA, fit in it: that is every texture of
+ *     at most 1 048 576 pixels (1024 x 1024, 2048 x 512, 1000 x 700 ...).  Anything larger is refused with
+ *     ROSY_TEX_ERR_ARG and a message that says so - use rosy_tex_mips_device with your own scratch for those;
+ *   - always the one-kernel-per-level path, never the fused TMA kernel (whose set-up probe allocates).  On extents
+ *     where rosy_tex_mips_device takes that path too (a side that is not a multiple of 64) the bytes are identical;
+ *     where it takes the fused kernel, each result is within 1 of the CPU oracle in every 8-bit channel (the bar
+ *     of the test suite), so the two can differ from one another by a unit or two in a few texels;
+ *   - the FIRST call on each device does a one-time set-up for that device (looks up the array's device address, loads
+ *     one 1 KB colour table, both synchronous).  Make that first call during start-up, outside any stream capture;
+ *     later calls only enqueue kernels on `stream`;
+ *   - all calls on a device share the array.  Nothing in it needs to be zero between calls (each level is written in
+ *     full before it is read, so stale contents of an earlier call are harmless), but two calls whose kernels can be
+ *     in flight on the same device at the same time - different streams, different threads - overwrite each other's
+ *     data and produce garbage.  Keep them on one stream, or order them with events. */
+#define ROSY_TEX_STATIC_SCRATCH_BYTES (5u * 1024u * 1024u + 256u)
+ROSY_TEX_API int rosy_tex_mips_device_static(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain,
+                                             void* stream);
+
 /* A batch of device-resident textures ("batched small textures per launch").
  * The mip chains of every texture whose extents are multiples of 64 are built by ONE kernel
  * launch per image kind (colour / normal map), so that small textures run at HBM speed instead

@@ -1750,6 +1750,105 @@ static int launch_mips_generic(const Chain& c, bool normal_map, int normalize, c
     return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
 
+// ------------------------------------------------------------------------------------------
+// Mip chain for callers that may not allocate device memory (rosy_tex_mips_device_static).
+//
+// The per-level kernels hand the fp32 working values of one level to the next through two
+// ping-pong buffers.  Everywhere else the caller brings that memory; here it is a fixed array
+// inside the library image, so the call needs no allocator at all.  The price: the array takes
+// ROSY_TEX_STATIC_SCRATCH_BYTES of HBM on every device that loads the library, for as long as
+// the process lives, and every call on a device works in the same bytes.
+//
+// g_static_scratch below is, as far as HOST code is concerned, only a handle for the symbol; its
+// value on the host is not a device address and must never reach a kernel.  mips_static_setup()
+// asks the runtime for the real address (cudaGetSymbolAddress) once per device and every launch
+// gets that pointer.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[ROSY_TEX_STATIC_SCRATCH_BYTES];
+
+namespace {
+struct StaticScratchState {
+    int ready = 0;          // 1 once the address below and the colour table are valid for this device
+    void* d_ptr = nullptr;  // device address of g_static_scratch on this device
+};
+StaticScratchState g_static_state[64];
+std::mutex g_static_mu;
+
+// once per device, with that device current: resolve the array's device address and upload the one table the
+// per-level kernels read (c_SRGB_TO_LINEAR; same values as mips_upload_tables writes, so either order is fine).
+// Nothing here allocates device or pinned memory.
+int mips_static_setup(int dev, void** d_ptr, const char** err) {
+    std::lock_guard<std::mutex> g(g_static_mu);
+    StaticScratchState& S = g_static_state[dev];
+    if (!S.ready) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess || major != 10) {
+            cudaGetLastError();
+            *err = "the current device is not an sm_100 (Blackwell B200) device (there is no CPU fallback)";
+            return ROSY_TEX_ERR_NO_DEVICE;
+        }
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            *err = e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned a null address";
+            return ROSY_TEX_ERR_CUDA;
+        }
+        float lut[256];
+        for (int i = 0; i < 256; i++) {  // Surface::load then Surface::toLinearFromSrgb of i/255 (row A5)
+            const float c = (float)i / 255.0f;
+            lut[i] = c <= 0.04045f ? c / 12.92f : powf((c + 0.055f) / 1.055f, 2.4f);
+        }
+        e = cudaMemcpyToSymbol(c_SRGB_TO_LINEAR, lut, sizeof lut);
+        if (e != cudaSuccess) {
+            *err = cudaGetErrorString(e);
+            return ROSY_TEX_ERR_CUDA;
+        }
+        S.d_ptr = p;
+        S.ready = 1;
+    }
+    *d_ptr = S.d_ptr;
+    return ROSY_TEX_OK;
+}
+}  // namespace
+
+// bytes of g_static_scratch the per-level kernels need for this chain (levels 1 and 2 as fp32 RGBA + the unused ticket)
+size_t mips_static_scratch_need(const Chain& c) {
+    const size_t l1 = c.levels > 1 ? (size_t)c.lv[1].w * c.lv[1].h * sizeof(float4) : 0;
+    const size_t l2 = c.levels > 2 ? (size_t)c.lv[2].w * c.lv[2].h * sizeof(float4) : 0;
+    return 256 + align256(l1) + align256(l2);
+}
+
+// Returns a rosy_tex_status; *launches = kernels enqueued on s; *err = static text for the caller's error string.
+// Always the per-level kernels (the fused kernel needs a probe that allocates).  Nothing in the array has to be zero
+// on entry: every level kernel writes each fp32 texel of its output buffer before the next launch reads it.
+int mips_static_launch(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba, uint8_t* d_chain,
+                       cudaStream_t s, int* launches, const char** err) {
+    *launches = 0;
+    *err = "";
+    if (mips_static_scratch_need(c) > (size_t)ROSY_TEX_STATIC_SCRATCH_BYTES) {
+        *err = "texture too large for the built-in scratch array (ROSY_TEX_STATIC_SCRATCH_BYTES): use rosy_tex_mips_device";
+        return ROSY_TEX_ERR_ARG;
+    }
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        cudaGetLastError();
+        *err = e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal above 63";
+        return e != cudaSuccess ? ROSY_TEX_ERR_NO_DEVICE : ROSY_TEX_ERR_ARG;
+    }
+    void* d_scratch = nullptr;
+    const int rc = mips_static_setup(dev, &d_scratch, err);
+    if (rc) return rc;
+    if (c.levels <= 1 && !normal_map) return ROSY_TEX_OK;  // a 1x1 colour image has no chain to build
+    const int n = launch_mips_generic(c, normal_map, normalize, d_rgba, d_chain, d_scratch, s);
+    if (n < 0) {
+        *err = cudaGetErrorString(cudaGetLastError());
+        return ROSY_TEX_ERR_CUDA;
+    }
+    *launches = n;
+    return ROSY_TEX_OK;
+}
+
 // Levels 0 .. mips_fused_encode_levels() - 1 of a BC5 / BC4 texture are encoded by the fused mip kernel itself when the
 // launch below is given the block stream; 0: the texture takes separate mip and encode launches.
 int mips_fused_encode_levels(const Chain& c, int format) {

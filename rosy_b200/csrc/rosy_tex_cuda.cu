@@ -1205,6 +1205,24 @@ int rosy_tex_encode_device(const rosy_tex_desc* desc, const void* d_rgba, void* 
                             d_scratch, static_cast<uint8_t*>(d_blocks), static_cast<cudaStream_t>(stream), true, true);
 }
 
+// The allocation-free variant of rosy_tex_mips_device (see the header).  Deliberately does NOT go through
+// ensure_init(): that creates streams and probes the device with a cudaMalloc.  The descriptor is resolved against
+// the configuration if rosy_tex_init() has run, else against the documented defaults.
+int rosy_tex_mips_device_static(const rosy_tex_desc* desc, const void* d_rgba, void* d_chain, void* stream) {
+    Resolved r;
+    int rc = resolve(desc, r);
+    if (rc) return rc;
+    if (!d_rgba || !d_chain) return fail(ROSY_TEX_ERR_ARG, "null device pointer");
+    if (misaligned(d_rgba, d_chain, nullptr, nullptr)) return fail(ROSY_TEX_ERR_ARG, "device pointers must be 16-byte aligned");
+    int launches = 0;
+    const char* err = "";
+    rc = mips_static_launch(make_chain(r.w, r.h), r.normal_map, r.normalize, static_cast<const uint8_t*>(d_rgba),
+                            static_cast<uint8_t*>(d_chain), static_cast<cudaStream_t>(stream), &launches, &err);
+    if (rc) return fail(rc, std::string("rosy_tex_mips_device_static: ") + err);
+    g_launches += (uint64_t)launches;
+    return ROSY_TEX_OK;
+}
+
 size_t rosy_tex_batch_scratch_size(int count) { return batch_desc_bytes(count); }
 
 }  // extern "C"

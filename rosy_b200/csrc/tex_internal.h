@@ -57,6 +57,11 @@ struct MipBatchItem {
     uint8_t* d_blocks = nullptr;
 };
 size_t mips_batch_desc_bytes(int n);
+// mip chain over the library's own fixed scratch array (no device allocation anywhere on the path); returns a
+// rosy_tex_status, *launches = kernels enqueued, *err = static message text
+size_t mips_static_scratch_need(const Chain& c);
+int mips_static_launch(const Chain& c, bool normal_map, int normalize, const uint8_t* d_rgba, uint8_t* d_chain,
+                       cudaStream_t s, int* launches, const char** err);
 int launch_mips_batch(int n, const MipBatchItem* items, void* d_desc, cudaStream_t s);
 // bc45_encode.cu
 int launch_bc45(const Chain& c, int first_level, int num_levels, bool bc5, const uint8_t* d_level0,

@@ -100,6 +100,7 @@ def lib():
                      "rosy_tex_submit_rgba8"):
             getattr(L, name).argtypes = [C.POINTER(Desc), C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.rosy_tex_mips_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 4
+        L.rosy_tex_mips_device_static.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 3
         L.rosy_tex_blocks_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 4
         L.rosy_tex_encode_device.argtypes = [C.POINTER(Desc)] + [C.c_void_p] * 5
         L.rosy_tex_batch_scratch_size.restype = C.c_size_t
@@ -281,6 +282,16 @@ def device_scratch_size(d):
 
 def mips_device(d, rgba_ptr, chain_ptr, scratch_ptr, stream=0):
     _check(lib().rosy_tex_mips_device(C.byref(d), rgba_ptr, chain_ptr, scratch_ptr, stream))
+
+
+STATIC_SCRATCH_BYTES = 5 * 1024 * 1024 + 256  # ROSY_TEX_STATIC_SCRATCH_BYTES
+
+
+def mips_device_static(d, rgba_ptr, chain_ptr, stream=0):
+    """rosy_tex_mips_device_static: the mip chain for callers that must not allocate device memory.  The
+    scratch is a fixed array inside the library (textures of at most 1024 x 1024 pixels); calls on one device
+    share it, so keep them on one stream."""
+    _check(lib().rosy_tex_mips_device_static(C.byref(d), rgba_ptr, chain_ptr, stream))
 
 
 def blocks_device(d, rgba_ptr, chain_ptr, blocks_ptr, stream=0):
