@@ -49,6 +49,25 @@ std::vector<uint8_t> rsy_image_table_bytes(const std::vector<asset_image>& image
 rosy::result write_rsy_image_table(const std::shared_ptr<rosy_logger::log>& l, const std::filesystem::path& asset_path,
                                    const std::vector<asset_image>& images) {
     const std::vector<uint8_t> bytes = rsy_image_table_bytes(images);
+    // Never replace a complete asset: if the target already is a .rsy that holds anything besides images (written by
+    // the reference's importer: materials, samplers, scenes, nodes or meshes, Asset.cpp:60-113), leave it alone.
+    if (FILE* old = std::fopen(asset_path.string().c_str(), "rb")) {
+        uint8_t head[128];
+        const size_t got = std::fread(head, 1, sizeof head, old);
+        std::fclose(old);
+        if (got == sizeof head && std::memcmp(head, "FYSR", 4) == 0) {
+            for (int k = 0; k < 6; k++) {
+                if (k == 4) continue;  // the image count
+                uint64_t n = 0;
+                std::memcpy(&n, head + 80 + 8 * k, 8);
+                if (n != 0) {
+                    l->error(std::format("refusing to overwrite {}: it holds a complete asset, not only an image table",
+                                         asset_path.string()));
+                    return rosy::result::error;
+                }
+            }
+        }
+    }
     FILE* stream = std::fopen(asset_path.string().c_str(), "wb");  // fopen_s in the reference (Windows only)
     if (!stream) {
         l->error(std::format("failed to open for writing {}", asset_path.string()));

@@ -29,6 +29,7 @@ struct asset_image {
 // six size_t counts {materials, samplers, scenes, nodes, images, meshes}; per image: size_t[2] {1, name chars},
 // uint32_t image_type, the name's chars.  Little endian, size_t = 8 bytes (the reference targets x64).
 std::vector<uint8_t> rsy_image_table_bytes(const std::vector<asset_image>& images);
+// Refuses (error) to replace an existing .rsy that holds anything besides images: that is a complete asset.
 [[nodiscard]] rosy::result write_rsy_image_table(const std::shared_ptr<rosy_logger::log>& l,
                                                  const std::filesystem::path& asset_path,
                                                  const std::vector<asset_image>& images);

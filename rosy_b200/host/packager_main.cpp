@@ -1,16 +1,19 @@
 // packager_main.cpp - a small CLI over the mirror, for exercising the boundary by hand:
 //   rosy_packager_tex [--normal|--srgb|--mr] <image> [...]      one generate_* call per image, serial
 //   rosy_packager_tex --queue [--normal|--srgb|--mr] <image> ... every image through the work queue
-//   rosy_packager_tex [--serial] [--dry-run] [--all-textures] <file.gltf>          the image part of `Packager.exe <file.gltf>`
+//   rosy_packager_tex [--serial] [--dry-run|--image-table] [--all-textures] <file.gltf>   the image part of `Packager.exe <file.gltf>`
 //       (Main.cpp:126-174 -> Gltf.cpp:97-286): every material image routed to its function, all in
 //       flight through the work queue (--serial: one after the other like the reference), and a
 //       <file>.textures.json manifest; --dry-run prints it only.
-//   rosy_packager_tex [--serial] [--dry-run] <file.fbx>        the image part of `Packager.exe <file.fbx>`
+//   rosy_packager_tex [--serial] [--dry-run|--image-table] <file.fbx>   the image part of `Packager.exe <file.fbx>`
 //       (Main.cpp:67-124 -> Fbx.cpp:421-474): the *normal.tga / *mixmap.tga / *albedo.tga next to the .fbx.
-// Both asset routes then write <file>.rsy holding the asset's IMAGE TABLE exactly as asset::write stores it
-// (Asset.cpp:39-113 header + sizes, :296-340 image records; asset_images.h) - with --dry-run too, which needs
-// no GPU.  N1 ends there: materials, nodes and meshes are written by the reference's importers, which need
-// fastgltf / the FBX SDK / MikkTSpace / meshoptimizer (absent here) and are outside the texture stage.
+// Both asset routes then write <file>.images.rsy holding the asset's IMAGE TABLE exactly as asset::write stores it
+// (Asset.cpp:39-113 header + sizes, :296-340 image records; asset_images.h).  The name is deliberately NOT <file>.rsy:
+// that is where the reference's importer puts the complete asset (Main.cpp:13-14) and a table with zero materials,
+// nodes and meshes must never replace it.  --dry-run writes nothing at all; --image-table writes the table only
+// (no image is conditioned, no GPU needed).  N1 ends there: materials, nodes and meshes are written by the reference's
+// importers, which need fastgltf / the FBX SDK / MikkTSpace / meshoptimizer (absent here) and are outside the
+// texture stage.
 // Exit code 0 / EXIT_FAILURE like Packager.exe (src/Packager/Main.cpp:143-173).
 #include <chrono>
 #include <cstdlib>
@@ -31,7 +34,7 @@ int main(int argc, char** argv) {
         l->error("Need to provide an image path");
         return EXIT_FAILURE;
     }
-    bool queue = false, serial = false, dry_run = false, all_textures = false;
+    bool queue = false, serial = false, dry_run = false, table_only = false, all_textures = false;
     int image_type = 0;  // Asset.h:109-112: 0 colour, 1 normal map, 2 metallic-roughness, 3 mixmap
     int done = 0;
     const auto start = std::chrono::system_clock::now();
@@ -41,7 +44,8 @@ int main(int argc, char** argv) {
         if (!std::strcmp(argv[i], "--srgb")) { image_type = 0; continue; }
         if (!std::strcmp(argv[i], "--mr")) { image_type = 2; continue; }
         if (!std::strcmp(argv[i], "--serial")) { serial = true; continue; }
-        if (!std::strcmp(argv[i], "--dry-run")) { dry_run = true; continue; }
+        if (!std::strcmp(argv[i], "--dry-run")) { dry_run = true; continue; }          // plan to stdout, no file is touched
+        if (!std::strcmp(argv[i], "--image-table")) { table_only = true; continue; }  // write <file>.images.rsy only
         if (!std::strcmp(argv[i], "--all-textures")) { all_textures = true; continue; }  // + emissive, occlusion (opt-in)
         if (std::filesystem::path(argv[i]).extension() == ".gltf") {
             // Main.cpp:10-65 load_gltf, image part
@@ -54,9 +58,12 @@ int main(int argc, char** argv) {
             for (const auto& job : plan.jobs)
                 if (job.image_index < images.size()) images[job.image_index].image_type = job.image_type;
             std::filesystem::path rsy{argv[i]};
-            rsy.replace_extension(".rsy");  // Main.cpp:13-14
+            rsy.replace_extension(".images.rsy");  // NOT Main.cpp:13-14's <file>.rsy: that one is the importer's
             if (dry_run) {
                 std::cout << manifest;
+                continue;
+            }
+            if (table_only) {
                 if (rosy_packager::write_rsy_image_table(l, rsy, images) != rosy::result::ok) return EXIT_FAILURE;
                 continue;
             }
@@ -71,16 +78,17 @@ int main(int argc, char** argv) {
         if (std::filesystem::path(argv[i]).extension() == ".fbx") {
             // Main.cpp:67-124 load_fbx, image part (Fbx.cpp:421-474)
             std::filesystem::path rsy{argv[i]};
-            rsy.replace_extension(".rsy");
+            rsy.replace_extension(".images.rsy");
             l->info(std::format("Parsing {} as {}", argv[i], rsy.string()));
             std::vector<rosy_packager::fbx_image_job> jobs;
             if (rosy_packager::plan_fbx_images(l, argv[i], jobs) != rosy::result::ok) return EXIT_FAILURE;
             std::vector<rosy_packager::asset_image> images;
-            if (dry_run) {
+            if (dry_run || table_only) {
                 for (const auto& job : jobs) {
                     images.push_back({job.image_type, job.dds_path.string()});
-                    std::cout << job.image_type << " " << job.source_path.string() << " -> " << job.dds_path.string() << "\n";
+                    if (dry_run) std::cout << job.image_type << " " << job.source_path.string() << " -> " << job.dds_path.string() << "\n";
                 }
+                if (dry_run) continue;
             } else if (rosy_packager::condition_fbx_images(l, jobs, serial, images) != rosy::result::ok) {
                 return EXIT_FAILURE;
             }

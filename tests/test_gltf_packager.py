@@ -144,9 +144,16 @@ def _parse_rsy(data):
 
 def test_rsy_image_table_bytes_for_gltf(tmp_path):
     p, names = _write_gltf(tmp_path, with_images=False)
+    # <file>.rsy belongs to the reference's importer (Main.cpp:13-14, the complete asset): this tool must never touch it
+    (tmp_path / "scene.rsy").write_bytes(b"the importer's complete asset")
+    before = sorted(os.listdir(tmp_path))
     out = subprocess.run([CLI, "--dry-run", str(p)], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr
-    data = (tmp_path / "scene.rsy").read_bytes()
+    assert sorted(os.listdir(tmp_path)) == before, "--dry-run must not write anything"
+    out = subprocess.run([CLI, "--image-table", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert (tmp_path / "scene.rsy").read_bytes() == b"the importer's complete asset"
+    data = (tmp_path / "scene.images.rsy").read_bytes()
     # hand-computed vector for the first bytes: 'RSYF' little endian, version 1, endianness 1, identity, root scene 0,
     # sizes {0,0,0,0,4,0}
     import struct
@@ -196,10 +203,23 @@ def test_fbx_image_routing_plan_and_rsy(tmp_path):
     # visited in file-name order; type 0 albedo, 3 mixmap, 1 normal (Fbx.cpp:450,459,468)
     want = [(0, "albedo.tga"), (0, "rock_albedo.tga"), (3, "rock_mixmap.tga"), (1, "rock_normal.tga")]
     assert [(int(l.split()[0]), os.path.basename(l.split(" -> ")[0].split(" ", 1)[1])) for l in lines] == want
-    r = _parse_rsy((tmp_path / "rock.rsy").read_bytes())
+    assert "image found:" in out.stdout + out.stderr
+    assert not (tmp_path / "rock.rsy").exists() and not (tmp_path / "rock.images.rsy").exists()  # a dry run writes nothing
+    out = subprocess.run([CLI, "--image-table", str(fbx)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    r = _parse_rsy((tmp_path / "rock.images.rsy").read_bytes())
     assert r["sizes"] == (0, 0, 0, 0, 4, 0)
     assert r["images"] == [(t, str(tmp_path / n.replace(".tga", ".dds"))) for t, n in want]
-    assert "image found:" in out.stdout + out.stderr
+    assert not (tmp_path / "rock.rsy").exists()
+    # a complete asset (any count besides the image count non-zero) under the target name is never replaced
+    import struct
+
+    full = bytearray((tmp_path / "rock.images.rsy").read_bytes())
+    struct.pack_into("<Q", full, 80 + 8 * 5, 3)  # pretend it holds 3 meshes
+    (tmp_path / "rock.images.rsy").write_bytes(bytes(full))
+    out = subprocess.run([CLI, "--image-table", str(fbx)], capture_output=True, text=True)
+    assert out.returncode != 0 and "refusing to overwrite" in out.stdout + out.stderr
+    assert (tmp_path / "rock.images.rsy").read_bytes() == bytes(full)
 
 
 @pytest.mark.gpu
@@ -215,7 +235,8 @@ def test_fbx_packager_run(tmp_path, serial, tex):
         got = np.fromfile(tmp_path / name.replace(".tga", ".dds"), dtype=np.uint8)
         assert (got == tex.encode_rgba8(img, kind)).all(), name
     assert not (tmp_path / "rock_height.dds").exists() and not (tmp_path / "albedo_rock.dds").exists()
-    assert len(_parse_rsy((tmp_path / "rock.rsy").read_bytes())["images"]) == 4
+    assert len(_parse_rsy((tmp_path / "rock.images.rsy").read_bytes())["images"]) == 4
+    assert not (tmp_path / "rock.rsy").exists()
     (tmp_path / "bad_normal.tga").write_bytes(b"\x00" * 10)
     out = subprocess.run([CLI, "--serial", str(fbx)], capture_output=True, text=True)
     assert out.returncode != 0
