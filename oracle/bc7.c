@@ -873,9 +873,12 @@ void oracle_encode_image(const uint8_t* rgba, int w, int h, int fmt, int quality
     }
     pthread_t tid[256];
     if (threads > 256) threads = 256;
-    for (int t = 1; t < threads; t++) pthread_create(&tid[t], NULL, encode_worker, &job);
+    char started[256];
+    /* the workers draw chunks from one counter: a thread that could not be created only means fewer helpers */
+    for (int t = 1; t < threads; t++) started[t] = pthread_create(&tid[t], NULL, encode_worker, &job) == 0;
     encode_worker(&job);
-    for (int t = 1; t < threads; t++) pthread_join(tid[t], NULL);
+    for (int t = 1; t < threads; t++)
+        if (started[t]) pthread_join(tid[t], NULL);
 }
 
 void oracle_decode_image(const uint8_t* blocks, int w, int h, int fmt, uint8_t* rgba) {

@@ -50,15 +50,22 @@ static void for_rows(row_fn fn, void* ctx, int rows, size_t elems_per_row) {
     }
     pthread_t tid[256];
     row_task task[256];
+    char started[256];
     for (int i = 0; i < n; i++) {
         task[i].fn = fn;
         task[i].ctx = ctx;
         task[i].y0 = (int)((long long)rows * i / n);
         task[i].y1 = (int)((long long)rows * (i + 1) / n);
-        if (i > 0) pthread_create(&tid[i], NULL, row_worker, &task[i]);
+        started[i] = i > 0 && pthread_create(&tid[i], NULL, row_worker, &task[i]) == 0;
     }
     row_worker(&task[0]);
-    for (int i = 1; i < n; i++) pthread_join(tid[i], NULL);
+    for (int i = 1; i < n; i++) {
+        /* no thread to be had (EAGAIN): the range is done here instead - a row range is never skipped */
+        if (started[i])
+            pthread_join(tid[i], NULL);
+        else
+            row_worker(&task[i]);
+    }
 }
 
 /* nvtt::Surface::countMipmaps, Packager.cpp:235 / :284 */
