@@ -265,6 +265,12 @@ ROSY_TEX_API long long rosy_tex_debug_faults(void);
 /* number of kernels this library has launched since load (all threads, all devices) */
 ROSY_TEX_API uint64_t rosy_tex_kernel_launches(void);
 
+/* Health of the work queue's device workers (no reference counterpart).  A worker whose DEVICE fails (not merely one
+ * texture) retires and its textures are finished by the others, so rosy_tex_wait_all can return 0 on a degraded
+ * pool; this is how to see it.  *live_workers: workers still serving the queue (-1: the queue has not started yet);
+ * *requeued: textures handed to another worker so far.  Either pointer may be NULL. */
+ROSY_TEX_API void rosy_tex_queue_status(int* live_workers, int* requeued);
+
 #ifdef __cplusplus
 }
 #endif

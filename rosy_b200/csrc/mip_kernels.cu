@@ -33,6 +33,7 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 #include <vector>
 
@@ -1491,8 +1492,8 @@ __global__ void smem_window_probe(unsigned int* out) {
     if (threadIdx.x == 0) *out = smem_u32(probe_raw);
 }
 struct DeviceMipState {
-    int window_ok = -1;                 // -1 unknown, 0 generic path only, 1 fused path usable
-    unsigned int* fault_host = nullptr; // mapped; non-zero after a fused launch that refused to run
+    std::atomic<int> window_ok{-1};     // -1 unknown, 0 generic path only, 1 fused path usable (read without the mutex)
+    unsigned int* fault_host = nullptr; // mapped; non-zero after a fused launch that refused to run (g_dev_mu)
 };
 DeviceMipState g_dev[64];
 std::mutex g_dev_mu;
@@ -1500,7 +1501,7 @@ std::mutex g_dev_mu;
 bool fused_window_ok() {
     int dev = 0;
     cudaGetDevice(&dev);
-    return g_dev[dev & 63].window_ok == 1;
+    return g_dev[dev & 63].window_ok.load(std::memory_order_acquire) == 1;
 }
 
 bool fused_ok(const Chain& c) {
@@ -1562,6 +1563,9 @@ bool fill_miptex(MipTex& T, const Chain& c, int normalize, const uint8_t* d_rgba
     return true;
 }
 
+#ifdef ROSY_TEX_TEST_HOOKS
+std::atomic<int> g_fake_layout_fault_left{getenv("ROSY_TEX_FAKE_LAYOUT_FAULT") && atoi(getenv("ROSY_TEX_FAKE_LAYOUT_FAULT")) ? 1 : 0};
+#endif
 template <bool NORMAL, int ENC>
 cudaError_t launch_fused_t(const MipTex* single, const MipTex* d_texs, const int* d_tile_base, int ntex,
                          int total_tiles, cudaStream_t s) {
@@ -1577,6 +1581,14 @@ cudaError_t launch_fused_t(const MipTex* single, const MipTex* d_texs, const int
     const int want = (total_tiles + GROUPS - 1) / GROUPS;  // every group of every CTA gets a tile
     const int grid = want < sms ? want : sms;
     mip_fused_kernel<NORMAL, ENC><<<grid, NTHREADS_TOTAL * GROUPS, FUSED_SMEM_BYTES, s>>>(*single, d_texs, d_tile_base, ntex, total_tiles);
+#ifdef ROSY_TEX_TEST_HOOKS
+    // ROSY_TEX_FAKE_LAYOUT_FAULT=1: the first fused launch of the process is reported like one that refused to run
+    // (the flag the kernel would have set through mapped memory is set from here)
+    if (g_fake_layout_fault_left.load() > 0 && g_fake_layout_fault_left.fetch_sub(1) == 1) {
+        std::lock_guard<std::mutex> g(g_dev_mu);
+        if (g_dev[dev & 63].fault_host) *static_cast<volatile unsigned int*>(g_dev[dev & 63].fault_host) = 1u;
+    }
+#endif
     return cudaGetLastError();
 }
 // enc: 0 mips only, 1 mips + BC5 of levels 0..4, 2 mips + BC4 of levels 0..4
@@ -1614,12 +1626,19 @@ long long mips_check_faults() {
 #endif
 }
 
-// true once a fused launch on the current device has refused to run (unexpected shared-window layout)
-bool mips_layout_fault() {
+// True if a fused launch on the current device has refused to run (unexpected shared-window layout) since the last
+// call.  Taking the fault also clears the flag and switches the device to the per-level kernels for good, so the
+// caller can simply run the texture again and later textures are not affected.
+bool mips_take_layout_fault() {
     int dev = 0;
     cudaGetDevice(&dev);
-    const DeviceMipState& D = g_dev[dev & 63];
-    return D.fault_host && *static_cast<volatile unsigned int*>(D.fault_host) != 0u;
+    std::lock_guard<std::mutex> g(g_dev_mu);
+    DeviceMipState& D = g_dev[dev & 63];
+    volatile unsigned int* flag = D.fault_host;
+    if (!flag || *flag == 0u) return false;
+    D.window_ok.store(0, std::memory_order_release);
+    *flag = 0u;
+    return true;
 }
 
 size_t mips_scratch_bytes(const Chain& c) {
@@ -1680,20 +1699,22 @@ int mips_upload_tables() {
         cudaGetDevice(&dev);
         std::lock_guard<std::mutex> g(g_dev_mu);
         DeviceMipState& D = g_dev[dev & 63];
-        if (D.window_ok < 0) {
-            D.window_ok = 0;
+        if (D.window_ok.load() < 0) {
+            int ok = 0;  // published once, below: fused_window_ok() reads window_ok without the mutex
             unsigned int* d_out = nullptr;
             unsigned int base = 0xFFFFFFFFu;
             if (cudaFuncSetAttribute(smem_window_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM_BYTES) == cudaSuccess &&
                 cudaMalloc(&d_out, 4) == cudaSuccess) {
                 smem_window_probe<<<1, 32, FUSED_SMEM_BYTES>>>(d_out);
                 if (cudaMemcpy(&base, d_out, 4, cudaMemcpyDeviceToHost) == cudaSuccess && (base & 0xFFFFu) == SMEM_WINDOW_BASE)
-                    D.window_ok = 1;
+                    ok = 1;
             }
             cudaFree(d_out);
             cudaGetLastError();
-            if (const char* e = getenv("ROSY_TEX_FAKE_WINDOW_MISMATCH"))  // test hook: behave as on a driver with another layout
-                if (atoi(e)) D.window_ok = 0;
+#ifdef ROSY_TEX_TEST_HOOKS  // librosy_tex_cuda_hooks.so only (`make hooks`): the product reads no fault-injection variables
+            if (const char* e = getenv("ROSY_TEX_FAKE_WINDOW_MISMATCH"))  // behave as on a driver with another layout
+                if (atoi(e)) ok = 0;
+#endif
             if (cudaHostAlloc(&D.fault_host, 4, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
                 *D.fault_host = 0u;
                 unsigned int* d_flag = nullptr;
@@ -1702,6 +1723,7 @@ int mips_upload_tables() {
             } else {
                 cudaGetLastError();
             }
+            D.window_ok.store(ok, std::memory_order_release);
         }
     }
     return cudaMemcpyToSymbol(g_SRGB_TO_LINEAR, lut, sizeof lut) == cudaSuccess &&

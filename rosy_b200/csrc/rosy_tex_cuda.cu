@@ -12,6 +12,7 @@
 #include <atomic>
 #include <condition_variable>
 #include <deque>
+#include <map>
 #include <algorithm>
 #include <mutex>
 #include <new>
@@ -120,7 +121,9 @@ struct State {
     std::deque<Slot> slots;  // deque: references stay valid when the queue adds its own slots
     std::vector<int> tables_ready;  // device ordinals with constant tables uploaded
     // work queue
-    std::deque<Job> queue;
+    // ordered largest texture first, submission order among equals: the pop below is O(log n) however long the backlog
+    std::map<std::pair<uint64_t, uint64_t>, Job> queue;  // key: (~pixels, sequence number)
+    uint64_t queue_seq = 0;
     std::vector<std::thread> workers;
     bool queue_batching = true;  // ROSY_TEX_QUEUE_BATCH=0: one texture per pass whatever its size
     int running = 0;
@@ -370,8 +373,14 @@ enum What { WHAT_DDS, WHAT_MIPS, WHAT_LEVEL };
 
 // host buffers in, host buffers out, on one slot
 int run_host_impl(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len);
+constexpr int RC_LAYOUT_RETRY = -100;  // internal: the fused mip kernel refused to run; the device now uses the per-level kernels
 int run_host(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, uint8_t* out, size_t cap, size_t* len) {
-    const int rc = run_host_impl(sl, r, what, rgba, out, cap, len);
+    int rc = run_host_impl(sl, r, what, rgba, out, cap, len);
+    if (rc == RC_LAYOUT_RETRY) {  // once more, on the generic path (mips_take_layout_fault switched the device over)
+        sl->ticket_dirty = true;
+        rc = run_host_impl(sl, r, what, rgba, out, cap, len);
+        if (rc == RC_LAYOUT_RETRY) rc = fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
+    }
     if (rc && rc != ROSY_TEX_ERR_ARG) sl->ticket_dirty = true;
     return rc;
 }
@@ -423,7 +432,7 @@ int run_host_impl(Slot* sl, const Resolved& r, What what, const uint8_t* rgba, u
         CU_TRY(cudaMemcpyAsync(out + ROSY_TEX_DDS_HEADER_BYTES, sl->d_blocks, blk_bytes, cudaMemcpyDeviceToHost, sl->stream));
     }
     CU_TRY(cudaStreamSynchronize(sl->stream));
-    if (mips_layout_fault()) return fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
+    if (mips_take_layout_fault()) return RC_LAYOUT_RETRY;
     return ROSY_TEX_OK;
 }
 
@@ -553,7 +562,8 @@ int run_host_batch(Slot* sl, std::vector<HostJob>& jobs) {
     }
     sl->ticket_dirty = true;  // until the batch is known to have run to its end
     CU_TRY(cudaStreamSynchronize(sl->stream));
-    if (mips_layout_fault()) return fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
+    // a refused fused launch: the caller (worker_main) runs the members one by one, which now take the per-level kernels
+    if (mips_take_layout_fault()) return fail(ROSY_TEX_ERR_CUDA, "fused mip kernel met an unexpected shared-memory window layout");
     // the single-texture path relies on a zero ticket at the start of d_scratch: still true (tickets return to zero)
     sl->ticket_dirty = false;
     return ROSY_TEX_OK;
@@ -644,21 +654,31 @@ void note_error_locked(State& s, int rc) {
 constexpr uint64_t BATCH_MEMBER_PX = 1u << 18, BATCH_TOTAL_PX = 4u << 20;
 constexpr size_t BATCH_MAX = 64;
 inline uint64_t job_px(const Job& j) { return (uint64_t)j.desc.width * j.desc.height; }
+// call with s.mu held
+inline void queue_push_locked(State& s, Job&& j) {
+    const std::pair<uint64_t, uint64_t> key{~job_px(j), s.queue_seq++};
+    s.queue.emplace(key, std::move(j));
+}
 
 // Pop order: largest texture first, so that the long jobs start early and the small ones fill
 // the gaps at the end (LPT).  Small textures are then taken together as described above.
-// Failure handling: a device-level failure (ROSY_TEX_ERR_CUDA / _NOMEM on the device) retires the
-// worker that saw it; its textures go back to the queue once and are finished by the remaining workers
-// (other slots / other devices).  When no worker is left, or a texture fails twice, the error is reported
-// by wait_all, which is the reference's behaviour: any failure aborts the asset (Gltf.cpp:225-229).
+// Failure handling: after a ROSY_TEX_ERR_CUDA the worker probes its device (cudaDeviceSynchronize).
+// A healthy device means the failure belongs to that texture (a refused launch, a tensor map that cannot be
+// built): the error is reported on it and the worker carries on.  A probe that fails too means the context is
+// gone (lost device, illegal address, ECC): the worker retires, frees its device buffers, says so on stderr, and
+// its textures go back to the queue once to be finished by the remaining workers (other devices).  When no
+// worker is left, or a texture fails twice, the error is reported by wait_all, which is the reference's
+// behaviour: any failure aborts the asset (Gltf.cpp:225-229).  rosy_tex_queue_status() shows a degraded pool.
 void worker_main(Slot* sl, int slot_index) {
     State& s = st();
     std::vector<Job> jobs;
     std::vector<HostJob> hj;
     std::vector<size_t> lens;
     std::vector<int> rcs;
-    int fault_left = 0;  // test hook: ROSY_TEX_FAULT_SLOT=<slot index> makes that worker's first pass fail like a lost device
+    int fault_left = 0;
+#ifdef ROSY_TEX_TEST_HOOKS  // librosy_tex_cuda_hooks.so only: ROSY_TEX_FAULT_SLOT=<slot index> makes that worker's first pass fail like a lost device
     if (const char* e = getenv("ROSY_TEX_FAULT_SLOT")) fault_left = atoi(e) == slot_index ? 1 : 0;
+#endif
     for (;;) {
         jobs.clear();
         {
@@ -667,29 +687,27 @@ void worker_main(Slot* sl, int slot_index) {
             if (s.stop && s.queue.empty()) return;
             const size_t live = s.live_workers > 0 ? (size_t)s.live_workers : 1;
             const size_t share = (s.queue.size() + live - 1) / live;
-            size_t big = 0;
-            for (size_t i = 1; i < s.queue.size(); i++)
-                if (job_px(s.queue[i]) > job_px(s.queue[big])) big = i;
-            jobs.push_back(std::move(s.queue[big]));
-            s.queue.erase(s.queue.begin() + (long)big);
+            jobs.push_back(std::move(s.queue.begin()->second));  // the largest texture waiting
+            s.queue.erase(s.queue.begin());
             uint64_t px = job_px(jobs[0]);
             // the largest one is small: so is everything else in the queue
             if (s.queue_batching && px <= BATCH_MEMBER_PX)
                 while (!s.queue.empty() && jobs.size() < share && jobs.size() < BATCH_MAX &&
-                       px + job_px(s.queue.front()) <= BATCH_TOTAL_PX) {
-                    px += job_px(s.queue.front());
-                    jobs.push_back(std::move(s.queue.front()));
-                    s.queue.pop_front();
+                       px + job_px(s.queue.begin()->second) <= BATCH_TOTAL_PX) {
+                    px += job_px(s.queue.begin()->second);
+                    jobs.push_back(std::move(s.queue.begin()->second));
+                    s.queue.erase(s.queue.begin());
                 }
             s.running += (int)jobs.size();
         }
         const size_t n = jobs.size();
         lens.assign(n, 0);
         rcs.assign(n, 0);
-        bool batched = false;
+        bool batched = false, injected = false;
         const int guard_rc = guarded([&] {
             if (fault_left > 0) {
                 fault_left--;
+                injected = true;
                 for (size_t i = 0; i < n; i++) rcs[i] = fail(ROSY_TEX_ERR_CUDA, "injected device fault (ROSY_TEX_FAULT_SLOT)");
                 return (int)ROSY_TEX_OK;
             }
@@ -724,15 +742,23 @@ void worker_main(Slot* sl, int slot_index) {
         if (guard_rc)
             for (size_t i = 0; i < n; i++) rcs[i] = rcs[i] ? rcs[i] : guard_rc;
         bool retire = false;
+        // is the device itself gone, or did only this texture fail?  (probed outside the lock: it waits for the device)
+        bool cuda_error = false, device_lost = false;
+        for (size_t i = 0; i < n; i++) cuda_error = cuda_error || rcs[i] == ROSY_TEX_ERR_CUDA;
+        if (cuda_error) {
+            device_lost = injected;
+            if (!injected) {
+                cudaSetDevice(sl->device);
+                device_lost = cudaDeviceSynchronize() != cudaSuccess;
+            }
+            cudaGetLastError();
+        }
         {
             std::lock_guard<std::mutex> g(s.mu);
-            // a device-level failure: hand the textures to the other workers (once per texture) and retire
-            bool device_fault = false;
-            for (size_t i = 0; i < n; i++) device_fault = device_fault || rcs[i] == ROSY_TEX_ERR_CUDA;
-            if (device_fault && s.live_workers > 1) {
+            // a lost device: hand the textures to the other workers (once per texture) and retire
+            if (device_lost && s.live_workers > 1) {
                 retire = true;
                 s.live_workers--;
-                cudaGetLastError();
             }
             for (size_t i = 0; i < n; i++) {
                 Job& job = jobs[i];
@@ -741,7 +767,7 @@ void worker_main(Slot* sl, int slot_index) {
                 if (retire && rc == ROSY_TEX_ERR_CUDA && job.attempts == 0) {
                     job.attempts++;
                     s.requeued++;
-                    s.queue.push_back(std::move(job));
+                    queue_push_locked(s, std::move(job));
                     continue;
                 }
                 note_error_locked(s, rc);
@@ -768,7 +794,23 @@ void worker_main(Slot* sl, int slot_index) {
             }
         }
         s.cv.notify_all();
-        if (retire) return;
+        if (retire) {
+            // give the device memory back (on a dead context these calls fail, which is fine) and make the loss visible
+            for (uint8_t** p : {&sl->d_in, &sl->d_chain, &sl->d_scratch, &sl->d_blocks, &sl->d_desc}) {
+                cudaFree(*p);
+                *p = nullptr;
+            }
+            sl->cap_in = sl->cap_chain = sl->cap_scratch = sl->cap_blocks = sl->cap_desc = 0;
+            cudaGetLastError();
+            int left;
+            {
+                std::lock_guard<std::mutex> g(s.mu);
+                left = s.live_workers;
+            }
+            fprintf(stderr, "rosy_tex: worker %d on device %d retired after a device fault; %d worker(s) left\n", slot_index,
+                    sl->device, left);
+            return;
+        }
     }
 }
 
@@ -867,7 +909,7 @@ void io_main() {
                 j.staged = rgba.size() + j.cap;
                 s.staged_bytes += j.staged;
                 j.dds_path = t.dds_path.empty() ? replace_extension(t.path, ".dds") : t.dds_path;  // Packager.cpp:231
-                s.queue.push_back(std::move(j));
+                queue_push_locked(s, std::move(j));
             }
         }
         s.cv.notify_all();
@@ -890,7 +932,7 @@ int enqueue(Job&& job) {
         std::lock_guard<std::mutex> g(s.mu);
         start_workers_locked(s);
         s.pending++;
-        s.queue.push_back(std::move(job));
+        queue_push_locked(s, std::move(job));
     }
     s.cv.notify_all();
     return ROSY_TEX_OK;
@@ -1291,5 +1333,12 @@ long long rosy_tex_debug_faults(void) {
 }
 
 uint64_t rosy_tex_kernel_launches(void) { return g_launches.load(); }
+
+void rosy_tex_queue_status(int* live_workers, int* requeued) {
+    State& s = st();
+    std::lock_guard<std::mutex> g(s.mu);
+    if (live_workers) *live_workers = s.workers.empty() ? -1 : s.live_workers;
+    if (requeued) *requeued = s.requeued;
+}
 
 }  // extern "C"

@@ -91,7 +91,9 @@ size_t bc7_batch_desc_bytes(int n);
 int launch_bc7_batch(int n, const Bc7BatchItem* items, void* d_desc, cudaStream_t s);
 int bc7_upload_tables();   // per device, once
 int mips_upload_tables();  // per device, once (also probes the shared-window layout the fused mip kernel needs)
-bool mips_layout_fault();
-long long mips_check_faults();  // ROSY_TEX_CHECKED builds: out-of-bounds stores counted so far on the current device; -1 otherwise  // a fused mip launch on the current device refused to run: its output is invalid
+// a fused mip launch on the current device refused to run since the last call (its output is invalid): clears the
+// flag and moves the device to the per-level kernels, so running the texture again succeeds
+bool mips_take_layout_fault();
+long long mips_check_faults();  // ROSY_TEX_CHECKED builds: out-of-bounds stores counted so far on the current device; -1 otherwise
 
 }  // namespace rosy_tex

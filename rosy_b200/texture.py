@@ -325,3 +325,10 @@ def debug_faults():
 
 def kernel_launches():
     return lib().rosy_tex_kernel_launches()
+
+
+def queue_status():
+    """(live_workers, requeued) of the work queue; live_workers is -1 before the first submit"""
+    a, b = C.c_int(0), C.c_int(0)
+    lib().rosy_tex_queue_status(C.byref(a), C.byref(b))
+    return a.value, b.value

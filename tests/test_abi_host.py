@@ -274,3 +274,14 @@ def test_png_suite_of_the_reference_tree(tex, oracle):
         assert got.shape == ref.shape and (got == ref).all(), f
         checked += 1
     assert checked >= 240
+
+
+def test_product_library_reads_no_fault_injection_variables():
+    """the hooks tests/ uses to fake a lost device or an unexpected shared-memory layout live in
+    librosy_tex_cuda_hooks.so only; an environment variable cannot make the shipping library fail"""
+    csrc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rosy_b200", "csrc")
+    product = open(os.path.join(csrc, "librosy_tex_cuda.so"), "rb").read()
+    hooks = open(os.path.join(csrc, "librosy_tex_cuda_hooks.so"), "rb").read()
+    for name in (b"ROSY_TEX_FAULT_SLOT\0", b"ROSY_TEX_FAKE_WINDOW_MISMATCH\0", b"ROSY_TEX_FAKE_LAYOUT_FAULT\0"):
+        assert name not in product, name
+        assert name in hooks, name

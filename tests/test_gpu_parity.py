@@ -7,6 +7,8 @@ Bars (north_star / SURVEY.md 8c):
     kernel implements the same search specification as the oracle, so we additionally require
     bit-exact blocks and report it separately from the PSNR gate.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -571,6 +573,12 @@ def test_opt_in_linear_data_maps_and_srgb_flag(tex, oracle, synth):
     assert (tex.encode_rgba8(col, tex.KIND_COLOR) == base_col).all()
 
 
+# the product built with -DROSY_TEX_TEST_HOOKS (`make -C rosy_b200/csrc hooks`): the only library that reads the
+# fault-injection variables; the tests that need them run it in a process of their own
+HOOKS_LIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rosy_b200", "csrc",
+                         "librosy_tex_cuda_hooks.so")
+
+
 def _run_py(code, env_extra):
     import os
     import subprocess
@@ -598,11 +606,19 @@ for _ in range(2):
 want = O.mip_chain(img, O.KIND_SRGB)
 print(max(int(np.abs(g.astype(int) - w.astype(int)).max()) for g, w in zip(got, want)), T.kernel_launches())
 """
-    worst, launches = map(int, _run_py(code, {"ROSY_TEX_FAKE_WINDOW_MISMATCH": "1"}).split()[-2:])
+    worst, launches = map(int, _run_py(code, {"ROSY_TEX_LIB": HOOKS_LIB, "ROSY_TEX_FAKE_WINDOW_MISMATCH": "1"}).split()[-2:])
     assert worst <= 1
     assert launches >= 2 * 9, "the per-level kernels must have run (one launch per level)"
     worst, launches = map(int, _run_py(code, {}).split()[-2:])
     assert worst <= 1 and launches == 2, "the fused kernel is one launch per chain"
+    # the product library has no such hook: the variable changes nothing there
+    worst, launches = map(int, _run_py(code, {"ROSY_TEX_FAKE_WINDOW_MISMATCH": "1"}).split()[-2:])
+    assert worst <= 1 and launches == 2
+    # ADVICE r2: a fused launch that refuses to run at run time (faked: the flag it would set is set after the first
+    # fused launch) costs that texture one re-run on the per-level kernels and moves the device to them for good -
+    # no error, nothing sticky: 1 refused fused launch + 9 per-level launches, then 9 for the second chain
+    worst, launches = map(int, _run_py(code, {"ROSY_TEX_LIB": HOOKS_LIB, "ROSY_TEX_FAKE_LAYOUT_FAULT": "1"}).split()[-2:])
+    assert worst <= 1 and launches == 1 + 9 + 9
 
 
 def test_device_fault_requeues_textures_on_the_remaining_workers():
@@ -617,8 +633,12 @@ q = T.Pending()
 for img, kind in imgs:
     q.submit(img, kind)
 outs = q.wait_all()
-print(hashlib.sha256(b"".join(o.tobytes() for o in outs)).hexdigest())
+live, requeued = T.queue_status()
+print(live, requeued, hashlib.sha256(b"".join(o.tobytes() for o in outs)).hexdigest())
 """
-    clean = _run_py(code, {}).split()[-1]
-    faulty = _run_py(code, {"ROSY_TEX_FAULT_SLOT": "0"}).split()[-1]
+    live, requeued, clean = _run_py(code, {}).split()[-3:]
+    assert (int(live), int(requeued)) == (2, 0)  # one B200, two workers, nothing went wrong
+    live, requeued, faulty = _run_py(code, {"ROSY_TEX_LIB": HOOKS_LIB, "ROSY_TEX_FAULT_SLOT": "0"}).split()[-3:]
     assert clean == faulty
+    # the degraded pool is visible: wait_all returned 0, but one worker is gone and its textures were handed over
+    assert int(live) == 1 and int(requeued) >= 1
