@@ -194,9 +194,9 @@ def run_reference_arm(args, rank):
     mpix = len(sample) * args.size * args.size / 1e6
     value = mpix / sec
     sec1 = cpu_oracle_run(sample, args.kind, fmt, q, threads=1)
+    # the same `config` as the GPU arm's line, key for key (the driver compares them); what this arm's bounded step
+    # covers is said in cpu_baseline.sample
     cfg = workload_config(args, args.textures)
-    cfg["sample"] = (f"each timed step of this arm is 1 of the workload's {args.textures} textures per GPU "
-                     "(bounded CPU sample; the metric is per pixel, so the value is comparable)")
     line = {
         "impl": "reference",
         "metric": METRIC,
@@ -218,7 +218,8 @@ def run_reference_arm(args, rank):
             "cores": cores,
             "value_1t": mpix / sec1,
             "kind": "port",
-            "sample": f"1 x {args.size}x{args.size} {args.kind}, full mips + {args.format.upper()} {args.quality}, per step; "
+            "sample": f"each timed step of this arm is 1 of the workload's {args.textures} textures per GPU (bounded CPU sample; the "
+            f"metric is per pixel, so the value is comparable): 1 x {args.size}x{args.size} {args.kind}, full mips + {args.format.upper()} {args.quality}; "
             "mip rows and blocks both shared by all host threads; value_1t = the same texture on 1 thread",
         },
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

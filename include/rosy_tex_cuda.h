@@ -125,7 +125,7 @@ ROSY_TEX_API const char* rosy_tex_last_error(void);
 ROSY_TEX_API const char* rosy_tex_status_string(int status);
 
 /* ---- 1:1 with the reference --------------------------------------------------------------
- * Read the image at image_path (PNG / TGA / PPM / raw .rgba8), build the full mip chain, block
+ * Read the image at image_path (PNG / JPEG baseline + progressive / TGA / PNM / raw .rgba8), build the full mip chain, block
  * compress every level and write <image_path with its extension replaced by ".dds"> with a
  * DDS + DX10 header.  Return 0 on success.  The path is borrowed.  The file is written under a
  * temporary name and renamed, so a failed call leaves no partial .dds behind.
@@ -139,7 +139,7 @@ ROSY_TEX_API int rosy_tex_generate_texture_file(const char* image_path, int kind
                                                 const char* dds_path);
 
 /* nvtt::Surface::load stand-in (Packager.cpp:222, :269), exposed so the decoder can be tested on
- * its own: decodes PNG / TGA / PNM / .rgba8 into a malloc'd RGBA8 buffer (free with
+ * its own: decodes PNG / JPEG / TGA / PNM / .rgba8 into a malloc'd RGBA8 buffer (free with
  * rosy_tex_free_image).  Host only; needs no device. */
 ROSY_TEX_API int rosy_tex_load_image(const char* image_path, uint8_t** rgba, uint32_t* width,
                                      uint32_t* height);
