@@ -196,6 +196,38 @@ def have_ref_dds():
     return _dds is not None
 
 
+_asset = _load_ref("libasset_ref.so")
+
+
+def have_ref_asset():
+    return _asset is not None
+
+
+def ref_asset_write_images(path, images):
+    """the reference's own asset::write (src/Asset/Asset.cpp:39-340) for an asset that holds only `images`
+    [(image_type, name), ...]; writes the .rsy at `path`"""
+    n = len(images)
+    types = (C.c_uint32 * max(n, 1))(*[int(t) for t, _ in images])
+    names = (C.c_char_p * max(n, 1))(*[nm.encode() for _, nm in images])
+    rc = _asset.ref_asset_write_images(str(path).encode(), n, types, names)
+    if rc != 0:
+        raise RuntimeError("asset::write failed")
+
+
+def ref_asset_read_images(path, max_images=256, name_stride=1024):
+    """the reference's own asset::read (Asset.cpp:409-848) on the .rsy at `path` ->
+    ([(image_type, name), ...], (materials, samplers, scenes, nodes, meshes)); None if it rejects the file"""
+    types = (C.c_uint32 * max_images)()
+    names = C.create_string_buffer(max_images * name_stride)
+    other = (C.c_uint64 * 5)()
+    n = _asset.ref_asset_read_images(str(path).encode(), max_images, types, names, name_stride, other)
+    if n < 0:
+        return None
+    raw = names.raw
+    out = [(int(types[i]), raw[i * name_stride:(i + 1) * name_stride].split(b"\0", 1)[0].decode()) for i in range(min(n, max_images))]
+    return out, tuple(int(x) for x in other)
+
+
 def ref_bc4_block(src16):
     s = np.ascontiguousarray(src16, dtype=np.uint8).reshape(16)
     out = np.zeros(8, dtype=np.uint8)
