@@ -432,6 +432,53 @@ def main():
         for p in host_in + host_out:
             L.rosy_tex_free_host(p)
 
+        # ---- the host-feed ceiling beside it (SURVEY 8d "Scaling"): bare cudaMemcpyAsync, no kernels, the same byte mix per
+        # texture (16 MiB up, 5.33 MiB down at 2048^2), pinned buffers, two streams, every rank at the same time.  What e2e
+        # could reach if the copies were all there is; tools/h2d_ceiling.cu is the same measurement without Python.
+        depth = 4
+        h_up = [torch.empty(in_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+        h_dn = [torch.empty(blk_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+        d_up = [torch.empty(in_bytes, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        d_dn = [torch.zeros(blk_bytes, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        s_up, s_dn = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+        def copy_round():
+            with torch.cuda.stream(s_up):
+                for k in range(depth):
+                    d_up[k].copy_(h_up[k], non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                for k in range(depth):
+                    h_dn[k].copy_(d_dn[k], non_blocking=True)
+            s_up.synchronize()
+            s_dn.synchronize()
+
+        copy_round()
+        barrier()
+        t0 = time.perf_counter()
+        rounds = 0
+        while time.perf_counter() - t0 < 1.0:
+            copy_round()
+            rounds += 1
+        csec = time.perf_counter() - t0
+        barrier()
+        up_gbs = rounds * depth * in_bytes / csec / 1e9
+        dn_gbs = rounds * depth * blk_bytes / csec / 1e9
+        if world > 1:
+            tot = torch.tensor([up_gbs, dn_gbs], dtype=torch.float64)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+            up_gbs, dn_gbs = float(tot[0]), float(tot[1])
+        ceiling_mpix = up_gbs * 1e9 / 4 / 1e6  # 4 bytes of level 0 per pixel go up
+        e2e["host_ceiling_gbs"] = up_gbs
+        e2e["host_ceiling"] = {
+            "h2d_gbs": up_gbs,
+            "d2h_gbs": dn_gbs,
+            "mpix_s": ceiling_mpix,
+            "e2e_frac_of_ceiling": e2e["value"] / ceiling_mpix,
+            "how": f"bare cudaMemcpyAsync from / to pinned memory on all {world} rank(s) at once, {in_bytes} B up + {blk_bytes} B down "
+            "per texture, no kernels, 1 s; sum over ranks",
+        }
+        del h_up, h_dn, d_up, d_dn
+
     # ---------------- e2e_files leg: image files -> .dds files through rosy_tex_submit -----------
     # (the reference interface itself: generate_*_texture(path), Packager.cpp:216,263; decode + write included)
     e2e_files = None
