@@ -120,6 +120,89 @@ def test_gltf_packager_run(tmp_path, serial, tex, oracle):
             assert info["format"] == 98 and info["numMips"] == 7
 
 
+def _mosaic(base, times):
+    """a (times x times) mosaic of flipped / rolled copies of `base`: a large texture without the minutes the noise
+    stack would take at 4096^2 (values are only moved, so a normal map stays a normal map)"""
+    rows = []
+    for j in range(times):
+        row = []
+        for i in range(times):
+            t = np.roll(base, (37 * (i + times * j) + 1, 53 * (i + times * j) + 3), axis=(0, 1))
+            if i & 1:
+                t = t[:, ::-1]
+            if j & 1:
+                t = t[::-1]
+            row.append(t)
+        rows.append(np.concatenate(row, axis=1))
+    return np.ascontiguousarray(np.concatenate(rows, axis=0))
+
+
+@pytest.mark.gpu
+def test_sponza_scale_gltf_one_packager_run_against_the_oracle(tmp_path, tex, oracle, synth):
+    """BASELINE.json configs[2] under test: one `rosy_packager_tex scene.gltf` run over a
+    Sponza-like material set - 23 materials x (albedo, normal, metallic-roughness) + a shared detail map = 70 images,
+    the 1K-4K mix scaled by 1/8 so that the CPU oracle's share stays well under a minute, square and 2:1, PNG and
+    JPEG - plus one full 4096^2 image of each kind.  Every .dds the run writes is checked against the ORACLE
+    (oracle.generate_texture on the decoded pixels) by the rules of the BASELINE-size parity tests: header equal,
+    every level's blocks bit-exact on identical pixels, mip levels within 1 LSB, PSNR within 0.1 dB.  The loop being
+    replaced: Gltf.cpp:209-285 (one generate_* call per image, BC7 Quality_Normal for all three kinds)."""
+    from PIL import Image
+
+    from test_gpu_parity import _full_size_parity
+
+    sizes = [(128, 128), (256, 256), (512, 512), (256, 128), (512, 256)]  # 1K, 2K, 4K, 2Kx1K, 4Kx2K at 1/8
+    images, textures, materials = [], [], []
+
+    def add(name, arr, jpeg=False, level=6):
+        im = Image.fromarray(arr)
+        if jpeg:
+            im.convert("RGB").save(tmp_path / name, quality=92)
+        else:
+            im.save(tmp_path / name, compress_level=level)
+        images.append({"uri": name})
+        textures.append({"source": len(images) - 1})
+        return len(textures) - 1
+
+    for m in range(23):
+        w, h = sizes[m % len(sizes)]
+        a = add(f"mat{m:02d}_albedo.{'jpg' if m % 3 == 0 else 'png'}", synth.albedo(w, h, m if m % 4 else 7), jpeg=m % 3 == 0)
+        n = add(f"mat{m:02d}_normal.png", synth.normal(w, h, m))
+        r = add(f"mat{m:02d}_orm.png", synth.make("metal_rough", w, h, m))
+        materials.append({"pbrMetallicRoughness": {"baseColorTexture": {"index": a}, "metallicRoughnessTexture": {"index": r}},
+                          "normalTexture": {"index": n}})
+    detail = add("shared_detail.png", synth.albedo(256, 256, 3))
+    materials.append({"pbrMetallicRoughness": {"baseColorTexture": {"index": detail}}})
+    big = {"albedo": _mosaic(synth.albedo(1024, 1024, 5), 4), "normal": _mosaic(synth.normal(1024, 1024, 2), 4),
+           "metal_rough": _mosaic(synth.make("metal_rough", 1024, 1024, 1), 4)}
+    ba = add("big_albedo.png", big["albedo"], level=0)
+    bn = add("big_normal.png", big["normal"], level=0)
+    br = add("big_orm.png", big["metal_rough"], level=0)
+    materials.append({"pbrMetallicRoughness": {"baseColorTexture": {"index": ba}, "metallicRoughnessTexture": {"index": br}},
+                      "normalTexture": {"index": bn}})
+    assert len(images) == 73
+    p = tmp_path / "sponza_like.gltf"
+    p.write_text(json.dumps({"asset": {"version": "2.0"}, "images": images, "textures": textures, "materials": materials}))
+
+    out = subprocess.run([CLI, str(p)], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    manifest = json.loads((tmp_path / "sponza_like.textures.json").read_text())
+    assert len(manifest["jobs"]) == 73
+    differing = total = 0
+    for j in manifest["jobs"]:
+        kind = {0: tex.KIND_COLOR, 1: tex.KIND_NORMAL_MAP, 2: tex.KIND_METALLIC_ROUGHNESS}[j["image_type"]]
+        name = os.path.basename(j["source"])
+        assert ("_normal." in name) == (kind == tex.KIND_NORMAL_MAP) and ("_orm." in name) == (kind == tex.KIND_METALLIC_ROUGHNESS)
+        img = tex.load_image(j["source"])  # the decoders are pinned against stb_image in test_abi_host.py
+        if name.startswith("big_") and not name.endswith(".jpg"):
+            assert (img == big[{"big_albedo.png": "albedo", "big_normal.png": "normal", "big_orm.png": "metal_rough"}[name]]).all()
+        dds = np.fromfile(j["dds"], dtype=np.uint8)
+        d, t = _full_size_parity(tex, oracle, img, kind, tex.FORMAT_BC7, tex.QUALITY_NORMAL, got=dds,
+                                 per_level_min_px=1024 if img.shape[0] >= 1024 else 16384)
+        differing += d
+        total += t
+    print(f"configs[2]-like run: 73 .dds files, {differing} of {total} blocks differ end to end (1-LSB mip differences)")
+
+
 # ---- .rsy image table (Asset.cpp:39-113, :296-340) and the FBX image routing (Fbx.cpp:421-474) -------------
 def _parse_rsy(data):
     """hand-written reader of what asset::write stores for an asset that holds only images"""
